@@ -1,0 +1,823 @@
+// ro_cuda.cu -- C ABI (include/ro_cuda.h) over the sm_100a waterfall kernels.
+//
+// Host-side restatement of the framing rules of FFTBackend::process
+// (reference src/FFTBackend.cpp:192-279): frame k covers samples
+// [k*hop, k*hop + bins); the first frame needs `bins` samples; a tail shorter
+// than a frame is carried to the next call and dropped at end of stream.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <stdarg.h>
+#include <algorithm>
+#include <deque>
+#include <new>
+#include <vector>
+
+#include "../../include/ro_cuda.h"
+#include "ro_kernels.cuh"
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char *fmt, ...)
+{
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(g_err, sizeof g_err, fmt, ap);
+	va_end(ap);
+	return code;
+}
+
+#define CU(call)                                                              \
+	do {                                                                      \
+		cudaError_t e_ = (call);                                              \
+		if (e_ != cudaSuccess)                                                \
+			return fail(RO_E_CUDA, "%s failed: %s (%s:%d)", #call,            \
+			            cudaGetErrorString(e_), __FILE__, __LINE__);          \
+	} while (0)
+
+typedef void (*fft_kernel_t)(const ro::WfParams);
+typedef void (*det_kernel_t)(const ro::DetParams);
+
+struct KernelChoice {
+	fft_kernel_t fn;
+	int threads;
+	size_t smem;
+	int log2nb;
+};
+
+template <int LOG2NB, int P, int R3, int MINB, bool PRE>
+KernelChoice pick(int fmt)
+{
+	KernelChoice k;
+	constexpr int NB = 1 << LOG2NB;
+	constexpr int PAD1 = (R3 < 16) ? R3 : 0;
+	k.threads = NB / P;
+	k.smem = sizeof(float2) * (size_t)(NB + P * PAD1);
+	k.log2nb = LOG2NB;
+	if (fmt == ro::FMT_INT16) k.fn = ro::wf_fft_kernel<LOG2NB, P, R3, ro::FMT_INT16, PRE, MINB>;
+	else k.fn = ro::wf_fft_kernel<LOG2NB, P, R3, ro::FMT_FLOAT32, PRE, MINB>;
+	return k;
+}
+
+bool choose_kernel(int log2n, int fmt, KernelChoice *out)
+{
+	switch (log2n) {
+	case 10: *out = pick<10, 16, 4, 12, false>(fmt); return true;
+	case 11: *out = pick<11, 16, 8, 6, false>(fmt); return true;
+	case 12: *out = pick<12, 16, 16, 3, false>(fmt); return true;
+	case 13: *out = pick<13, 32, 8, 2, false>(fmt); return true;
+	case 14: *out = pick<14, 32, 16, 1, false>(fmt); return true;
+	default:
+		if (log2n > 14 && log2n <= 19) { *out = pick<14, 32, 16, 1, true>(fmt); return true; }
+		return false;
+	}
+}
+
+struct Pending {            // one submitted batch of the streaming path
+	uint64_t first_row;
+	size_t   n_rows;
+	size_t   consumed;
+	int      slot;          // -1: already moved to host vectors
+	cudaEvent_t done;
+	std::vector<float> rows;
+	std::vector<ro_det_rec> det;
+};
+
+}  // namespace
+
+struct ro_wf {
+	ro_wf_config cfg;
+	int N, log2n, overlap, hop, fmt;      // fmt: device encoding (int16 / float32)
+	int in_bytes;                         // bytes per complex sample on the device
+	int row_width;
+	int n_sms;
+	bool det_on;
+	KernelChoice kc;
+	int grid_cap;                         // resident CTAs for the persistent grid
+	det_kernel_t det_fn;
+
+	float  *d_window;
+	float2 *d_tw;
+
+	cudaStream_t own_stream, h2d_stream, d2h_stream;
+	cudaStream_t user_stream;
+	bool use_user_stream;
+
+	// profiling
+	bool profiling;
+	std::vector<cudaEvent_t> ev_pool;
+	std::vector<std::pair<cudaEvent_t, cudaEvent_t> > ev_used[2];
+	uint64_t launches;
+
+	// batch path (process_host) work space
+	size_t chunk_frames;
+	void  *d_in[2];
+	float *d_rows[2];
+	ro_det_rec *d_det[2];
+	size_t d_in_bytes, d_rows_bytes;
+	cudaEvent_t ev_h2d[2], ev_comp[2], ev_d2h[2];
+
+	// streaming path
+	size_t batch_frames;                  // submit threshold
+	size_t stage_cap;                     // samples per staging slot
+	unsigned char *h_stage[2];            // pinned input staging
+	void  *d_sin[2];                      // device input ping-pong (carry + new)
+	float *d_srows[2];                    // device rows per slot (full rows)
+	ro_det_rec *d_sdet[2];
+	float *h_srows[2];                    // pinned host rows per slot (row_width)
+	ro_det_rec *h_sdet[2];
+	cudaEvent_t ev_slot[2];
+	size_t slot_rows_cap;
+	int    cur;                           // slot being filled
+	size_t staged;                        // new samples in h_stage[cur]
+	size_t carry;                         // samples already on device at the front of d_sin[cur]
+	uint64_t next_row;                    // global index of the next frame
+	std::deque<Pending*> pending;
+	bool sticky_error;
+};
+
+// ---------------------------------------------------------------------------
+// host tables
+// ---------------------------------------------------------------------------
+extern "C" int ro_window_table(int32_t bins, float *out)
+{
+	if (bins < 2 || !out) return fail(RO_E_INVALID, "ro_window_table: bad arguments");
+	// reference src/FFTBackend.cpp:155-186: float coefficients, double angle and
+	// cosine, one rounding to float.  PI = 4*atan(1) (src/FFTBackend.cpp:100).
+	const double PI = 4.0 * atan(1.0);
+	const float a0 = 0.355768f, a1 = 0.487396f, a2 = 0.144232f, a3 = 0.012604f;
+	for (int i = 0; i < bins; i++) {
+		out[i] = (float)(a0
+		         - a1 * cos(2.0 * PI * (float)i / (float)(bins - 1))
+		         + a2 * cos(4.0 * PI * (float)i / (float)(bins - 1))
+		         - a3 * cos(6.0 * PI * (float)i / (float)(bins - 1)));
+	}
+	return RO_OK;
+}
+
+extern "C" int ro_twiddle_table(int32_t n, float *out)
+{
+	if (n < 1 || !out) return fail(RO_E_INVALID, "ro_twiddle_table: bad arguments");
+	const long double two_pi = 8.0L * atanl(1.0L);
+	for (int j = 0; j < n; j++) {
+		// reduce to the first octant so every entry is rounded from an argument <= pi/4
+		int q = (int)(((long long)j * 8) / n);          // octant 0..7
+		long double a;
+		float c, s;
+		long long r = (long long)j * 8 - (long long)q * n;   // j/n - q/8 = r/(8n)
+		a = two_pi * (long double)r / (8.0L * (long double)n);
+		long double ca = cosl(a), sa = sinl(a);
+		if (q & 1) {                                   // angle = (q+1)*pi/4 - (pi/4 - a)
+			long double b = two_pi / 8.0L - a;
+			ca = cosl(b); sa = sinl(b);
+			// cos((q+1)pi/4 - b), sin(...) with (q+1) even -> multiples of pi/2
+			int m = ((q + 1) / 2) & 3;
+			long double cc, ss;
+			switch (m) {
+			case 0: cc = ca;  ss = -sa; break;         // angle = -b
+			case 1: cc = sa;  ss = ca;  break;         // pi/2 - b
+			case 2: cc = -ca; ss = sa;  break;         // pi - b
+			default: cc = -sa; ss = -ca; break;        // 3pi/2 - b
+			}
+			c = (float)cc; s = (float)ss;
+		} else {
+			int m = (q / 2) & 3;                       // angle = m*pi/2 + a
+			long double cc, ss;
+			switch (m) {
+			case 0: cc = ca;  ss = sa;  break;
+			case 1: cc = -sa; ss = ca;  break;
+			case 2: cc = -ca; ss = -sa; break;
+			default: cc = sa; ss = -ca; break;
+			}
+			c = (float)cc; s = (float)ss;
+		}
+		out[2 * j] = c;
+		out[2 * j + 1] = -s;                           // exp(-i*theta)
+	}
+	return RO_OK;
+}
+
+extern "C" const char *ro_last_error(void) { return g_err; }
+extern "C" const char *ro_version(void) { return "radio_observer_b200 0.1 (sm_100a)"; }
+
+// ---------------------------------------------------------------------------
+// device helpers
+// ---------------------------------------------------------------------------
+extern "C" int ro_dev_count(int *n)
+{
+	if (!n) return fail(RO_E_INVALID, "ro_dev_count: null");
+	CU(cudaGetDeviceCount(n));
+	return RO_OK;
+}
+extern "C" int ro_dev_alloc(int device, size_t bytes, void **d_ptr)
+{
+	if (!d_ptr) return fail(RO_E_INVALID, "ro_dev_alloc: null");
+	CU(cudaSetDevice(device));
+	CU(cudaMalloc(d_ptr, bytes ? bytes : 1));
+	return RO_OK;
+}
+extern "C" int ro_dev_free(int device, void *d_ptr)
+{
+	CU(cudaSetDevice(device));
+	CU(cudaFree(d_ptr));
+	return RO_OK;
+}
+extern "C" int ro_dev_upload(int device, void *d_dst, const void *src, size_t bytes)
+{
+	CU(cudaSetDevice(device));
+	CU(cudaMemcpy(d_dst, src, bytes, cudaMemcpyHostToDevice));
+	return RO_OK;
+}
+extern "C" int ro_dev_download(int device, void *dst, const void *d_src, size_t bytes)
+{
+	CU(cudaSetDevice(device));
+	CU(cudaMemcpy(dst, d_src, bytes, cudaMemcpyDeviceToHost));
+	return RO_OK;
+}
+extern "C" int ro_dev_memset(int device, void *d_dst, int value, size_t bytes)
+{
+	CU(cudaSetDevice(device));
+	CU(cudaMemset(d_dst, value, bytes));
+	return RO_OK;
+}
+extern "C" int ro_host_alloc_pinned(size_t bytes, void **ptr)
+{
+	if (!ptr) return fail(RO_E_INVALID, "ro_host_alloc_pinned: null");
+	CU(cudaMallocHost(ptr, bytes ? bytes : 1));
+	return RO_OK;
+}
+extern "C" int ro_host_free_pinned(void *ptr)
+{
+	CU(cudaFreeHost(ptr));
+	return RO_OK;
+}
+
+// ---------------------------------------------------------------------------
+// lifecycle
+// ---------------------------------------------------------------------------
+namespace {
+
+cudaStream_t batch_stream(ro_wf *h) { return h->use_user_stream ? h->user_stream : h->own_stream; }
+
+int get_event(ro_wf *h, cudaEvent_t *ev)
+{
+	if (!h->ev_pool.empty()) {
+		*ev = h->ev_pool.back();
+		h->ev_pool.pop_back();
+		return RO_OK;
+	}
+	CU(cudaEventCreate(ev));
+	return RO_OK;
+}
+
+// Launch the fused kernel over n_frames frames of d_iq on stream s.
+int launch_fft(ro_wf *h, cudaStream_t s, const void *d_iq, float *d_rows, long long row_stride,
+               long long n_frames)
+{
+	if (n_frames <= 0) return RO_OK;
+	ro::WfParams p;
+	p.iq = d_iq;
+	p.window = h->d_window;
+	p.tw = h->d_tw;
+	p.rows = d_rows;
+	p.n_frames = n_frames;
+	p.hop = h->hop;
+	p.row_stride = row_stride;
+	p.iq_gain = (float)h->cfg.iq_gain;
+	p.log2n = h->log2n;
+	p.log2na = h->log2n - h->kc.log2nb;
+	const long long items = n_frames << p.log2na;
+	const int grid = (int)std::min<long long>(items, h->grid_cap);
+	cudaEvent_t e0 = 0, e1 = 0;
+	if (h->profiling) {
+		int rc = get_event(h, &e0); if (rc) return rc;
+		rc = get_event(h, &e1); if (rc) return rc;
+		CU(cudaEventRecord(e0, s));
+	}
+	h->kc.fn<<<grid, h->kc.threads, h->kc.smem, s>>>(p);
+	CU(cudaGetLastError());
+	h->launches++;
+	if (h->profiling) {
+		CU(cudaEventRecord(e1, s));
+		h->ev_used[0].push_back(std::make_pair(e0, e1));
+	}
+	return RO_OK;
+}
+
+int launch_detect(ro_wf *h, cudaStream_t s, const float *d_rows, long long row_stride,
+                  long long n_rows, ro_det_rec *d_det)
+{
+	if (n_rows <= 0 || !h->det_on || !d_det) return RO_OK;
+	ro::DetParams p;
+	p.rows = d_rows;
+	p.row_stride = row_stride;
+	p.n_rows = n_rows;
+	p.bins = h->N;
+	p.det_lo = h->cfg.det_lo;
+	p.det_w = h->cfg.det_w;
+	p.noise_lo = h->cfg.noise_lo;
+	p.noise_w = h->cfg.noise_w;
+	p.avg_bins = h->cfg.avg_bins;
+	p.out = reinterpret_cast<float4 *>(d_det);
+	const int wpb = 4;                                  // warps per block
+	long long blocks = (n_rows + wpb - 1) / wpb;
+	const long long cap = (long long)h->n_sms * 16;
+	if (blocks > cap) blocks = cap;
+	cudaEvent_t e0 = 0, e1 = 0;
+	if (h->profiling) {
+		int rc = get_event(h, &e0); if (rc) return rc;
+		rc = get_event(h, &e1); if (rc) return rc;
+		CU(cudaEventRecord(e0, s));
+	}
+	h->det_fn<<<(int)blocks, wpb * 32, 0, s>>>(p);
+	CU(cudaGetLastError());
+	h->launches++;
+	if (h->profiling) {
+		CU(cudaEventRecord(e1, s));
+		h->ev_used[1].push_back(std::make_pair(e0, e1));
+	}
+	return RO_OK;
+}
+
+void free_all(ro_wf *h)
+{
+	if (!h) return;
+	cudaSetDevice(h->cfg.device);
+	for (Pending *p : h->pending) { if (p->done) cudaEventDestroy(p->done); delete p; }
+	h->pending.clear();
+	for (int i = 0; i < 2; i++) {
+		cudaFree(h->d_in[i]); cudaFree(h->d_rows[i]); cudaFree(h->d_det[i]);
+		cudaFree(h->d_sin[i]); cudaFree(h->d_srows[i]); cudaFree(h->d_sdet[i]);
+		if (h->h_stage[i]) cudaFreeHost(h->h_stage[i]);
+		if (h->h_srows[i]) cudaFreeHost(h->h_srows[i]);
+		if (h->h_sdet[i]) cudaFreeHost(h->h_sdet[i]);
+		if (h->ev_h2d[i]) cudaEventDestroy(h->ev_h2d[i]);
+		if (h->ev_comp[i]) cudaEventDestroy(h->ev_comp[i]);
+		if (h->ev_d2h[i]) cudaEventDestroy(h->ev_d2h[i]);
+		if (h->ev_slot[i]) cudaEventDestroy(h->ev_slot[i]);
+		for (auto &pr : h->ev_used[i]) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+	}
+	for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
+	cudaFree(h->d_window);
+	cudaFree(h->d_tw);
+	if (h->own_stream) cudaStreamDestroy(h->own_stream);
+	if (h->h2d_stream) cudaStreamDestroy(h->h2d_stream);
+	if (h->d2h_stream) cudaStreamDestroy(h->d2h_stream);
+	delete h;
+}
+
+}  // namespace
+
+extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
+{
+	if (!cfg || !out) return fail(RO_E_INVALID, "ro_wf_create: null argument");
+	*out = NULL;
+	const int N = cfg->bins;
+	if (N < 1024 || N > 524288 || (N & (N - 1)))
+		return fail(RO_E_INVALID, "bins = %d: must be a power of two in [1024, 524288]", N);
+	if (cfg->iq_phase_shift != 0)
+		return fail(RO_E_INVALID, "iq_phase_shift = %d is not supported (the reference path "
+		            "src/FFTBackend.cpp:53-92 is ill-defined for non-zero shifts)", cfg->iq_phase_shift);
+	if (cfg->in_format < RO_IN_INT16 || cfg->in_format > RO_IN_COMPLEX64)
+		return fail(RO_E_INVALID, "in_format = %d", cfg->in_format);
+	if (cfg->n_bands < 0 || cfg->n_bands > RO_MAX_BANDS)
+		return fail(RO_E_INVALID, "n_bands = %d", cfg->n_bands);
+	int width = 0;
+	for (int b = 0; b < cfg->n_bands; b++) {
+		if (cfg->band_lo[b] < 0 || cfg->band_hi[b] > N || cfg->band_lo[b] >= cfg->band_hi[b])
+			return fail(RO_E_INVALID, "band %d = [%d, %d) outside [0, %d)", b, cfg->band_lo[b], cfg->band_hi[b], N);
+		width += cfg->band_hi[b] - cfg->band_lo[b];
+	}
+	const bool det_on = cfg->det_w > 0;
+	if (det_on) {
+		if (cfg->det_lo < 0 || cfg->det_lo + cfg->det_w > N || cfg->noise_lo < 0 || cfg->noise_w < 1 ||
+		    cfg->noise_lo + cfg->noise_w > N || cfg->avg_bins < 1)
+			return fail(RO_E_INVALID, "detector bands outside the row (det [%d,+%d) noise [%d,+%d) avg %d)",
+			            cfg->det_lo, cfg->det_w, cfg->noise_lo, cfg->noise_w, cfg->avg_bins);
+	}
+	int ndev = 0;
+	CU(cudaGetDeviceCount(&ndev));
+	if (cfg->device < 0 || cfg->device >= ndev)
+		return fail(RO_E_INVALID, "device %d of %d", cfg->device, ndev);
+	CU(cudaSetDevice(cfg->device));
+
+	ro_wf *h = new (std::nothrow) ro_wf();
+	if (!h) return fail(RO_E_NOMEM, "out of memory");
+	h->cfg = *cfg;
+	h->N = N;
+	h->log2n = ro::ilog2(N);
+	int ov = cfg->overlap;
+	if (ov < 0) ov = 0;                       // src/FFTBackend.cpp:108-109
+	if (ov >= N) ov = N - 1;
+	h->overlap = ov;
+	h->hop = N - ov;
+	h->fmt = cfg->in_format == RO_IN_INT16 ? ro::FMT_INT16 : ro::FMT_FLOAT32;
+	h->in_bytes = h->fmt == ro::FMT_INT16 ? 4 : 8;
+	h->row_width = cfg->n_bands ? width : N;
+	h->det_on = det_on;
+	if (!choose_kernel(h->log2n, h->fmt, &h->kc)) { free_all(h); return fail(RO_E_INVALID, "no kernel for bins = %d", N); }
+
+	cudaDeviceProp prop;
+	cudaError_t e = cudaGetDeviceProperties(&prop, cfg->device);
+	if (e != cudaSuccess) { free_all(h); return fail(RO_E_CUDA, "cudaGetDeviceProperties: %s", cudaGetErrorString(e)); }
+	h->n_sms = prop.multiProcessorCount;
+	e = cudaFuncSetAttribute((const void *)h->kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->kc.smem);
+	if (e != cudaSuccess) { free_all(h); return fail(RO_E_CUDA, "kernel image unusable on device %d (%s): %s; this library is built for sm_100a only", cfg->device, prop.name, cudaGetErrorString(e)); }
+	int occ = 0;
+	e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void *)h->kc.fn, h->kc.threads, h->kc.smem);
+	if (e != cudaSuccess || occ < 1) { free_all(h); return fail(RO_E_CUDA, "occupancy query failed: %s", cudaGetErrorString(e)); }
+	h->grid_cap = occ * h->n_sms;
+
+	{   // detector variant by noise band width
+		const int epl = (cfg->noise_w + 31) / 32;
+		if (!det_on) h->det_fn = ro::wf_detect_kernel<0>;
+		else if (epl <= 2) h->det_fn = ro::wf_detect_kernel<2>;
+		else if (epl <= 4) h->det_fn = ro::wf_detect_kernel<4>;
+		else if (epl <= 8) h->det_fn = ro::wf_detect_kernel<8>;
+		else if (epl <= 16) h->det_fn = ro::wf_detect_kernel<16>;
+		else if (epl <= 32) h->det_fn = ro::wf_detect_kernel<32>;
+		else h->det_fn = ro::wf_detect_kernel<0>;
+	}
+
+	// tables
+	std::vector<float> win(N), tw(2 * (size_t)N);
+	ro_window_table(N, win.data());
+	ro_twiddle_table(N, tw.data());
+#define CUH(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { free_all(h); \
+	return fail(RO_E_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); } } while (0)
+	CUH(cudaMalloc(&h->d_window, sizeof(float) * N));
+	CUH(cudaMalloc(&h->d_tw, sizeof(float2) * N));
+	CUH(cudaMemcpy(h->d_window, win.data(), sizeof(float) * N, cudaMemcpyHostToDevice));
+	CUH(cudaMemcpy(h->d_tw, tw.data(), sizeof(float2) * N, cudaMemcpyHostToDevice));
+	CUH(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+	CUH(cudaStreamCreateWithFlags(&h->h2d_stream, cudaStreamNonBlocking));
+	CUH(cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking));
+	for (int i = 0; i < 2; i++) {
+		CUH(cudaEventCreateWithFlags(&h->ev_h2d[i], cudaEventDisableTiming));
+		CUH(cudaEventCreateWithFlags(&h->ev_comp[i], cudaEventDisableTiming));
+		CUH(cudaEventCreateWithFlags(&h->ev_d2h[i], cudaEventDisableTiming));
+		CUH(cudaEventCreateWithFlags(&h->ev_slot[i], cudaEventDisableTiming));
+	}
+	h->batch_frames = cfg->max_batch_frames > 0 ? (size_t)cfg->max_batch_frames : 64;
+	*out = h;
+	return RO_OK;
+}
+
+extern "C" void ro_wf_destroy(ro_wf *h) { free_all(h); }
+
+extern "C" int ro_wf_row_width(const ro_wf *h) { return h ? h->row_width : 0; }
+extern "C" int ro_wf_overlap(const ro_wf *h) { return h ? h->overlap : 0; }
+
+extern "C" size_t ro_wf_frame_count(const ro_wf *h, size_t n_samples)
+{
+	if (!h || n_samples < (size_t)h->N) return 0;
+	return (n_samples - (size_t)h->N) / (size_t)h->hop + 1;
+}
+
+extern "C" int ro_wf_set_stream(ro_wf *h, void *cuda_stream)
+{
+	if (!h) return fail(RO_E_INVALID, "null handle");
+	h->user_stream = (cudaStream_t)cuda_stream;
+	h->use_user_stream = cuda_stream != NULL;
+	return RO_OK;
+}
+
+extern "C" int ro_wf_sync(ro_wf *h)
+{
+	if (!h) return fail(RO_E_INVALID, "null handle");
+	CU(cudaSetDevice(h->cfg.device));
+	CU(cudaStreamSynchronize(batch_stream(h)));
+	CU(cudaStreamSynchronize(h->h2d_stream));
+	CU(cudaStreamSynchronize(h->d2h_stream));
+	return RO_OK;
+}
+
+extern "C" int ro_wf_set_profiling(ro_wf *h, int enable)
+{
+	if (!h) return fail(RO_E_INVALID, "null handle");
+	h->profiling = enable != 0;
+	return RO_OK;
+}
+
+extern "C" int ro_wf_kernel_times(ro_wf *h, double ms_sum[2], uint64_t launches[2])
+{
+	if (!h) return fail(RO_E_INVALID, "null handle");
+	CU(cudaSetDevice(h->cfg.device));
+	CU(cudaDeviceSynchronize());
+	for (int k = 0; k < 2; k++) {
+		double sum = 0.0;
+		for (auto &pr : h->ev_used[k]) {
+			float ms = 0.f;
+			CU(cudaEventElapsedTime(&ms, pr.first, pr.second));
+			sum += ms;
+			h->ev_pool.push_back(pr.first);
+			h->ev_pool.push_back(pr.second);
+		}
+		if (ms_sum) ms_sum[k] = sum;
+		if (launches) launches[k] = h->ev_used[k].size();
+		h->ev_used[k].clear();
+	}
+	return RO_OK;
+}
+
+extern "C" uint64_t ro_wf_launch_count(const ro_wf *h) { return h ? h->launches : 0; }
+
+// ---------------------------------------------------------------------------
+// batch paths
+// ---------------------------------------------------------------------------
+extern "C" int ro_wf_process_resident(ro_wf *h, const void *d_iq, size_t n_samples,
+                                      float *d_rows, ro_det_rec *d_det,
+                                      size_t max_frames, size_t *n_frames, int sync)
+{
+	if (!h || !d_iq || !d_rows) return fail(RO_E_INVALID, "ro_wf_process_resident: null argument");
+	if (h->cfg.in_format == RO_IN_COMPLEX64)
+		return fail(RO_E_INVALID, "device-resident input must be int16 or float32");
+	CU(cudaSetDevice(h->cfg.device));
+	size_t F = ro_wf_frame_count(h, n_samples);
+	if (F > max_frames) F = max_frames;
+	if (n_frames) *n_frames = F;
+	cudaStream_t s = batch_stream(h);
+	int rc = launch_fft(h, s, d_iq, d_rows, h->N, (long long)F);
+	if (rc) return rc;
+	rc = launch_detect(h, s, d_rows, h->N, (long long)F, d_det);
+	if (rc) return rc;
+	if (sync) CU(cudaStreamSynchronize(s));
+	return RO_OK;
+}
+
+extern "C" int ro_wf_detect_resident(ro_wf *h, const float *d_rows, size_t n_rows,
+                                     ro_det_rec *d_det, int sync)
+{
+	if (!h || !d_rows || !d_det) return fail(RO_E_INVALID, "ro_wf_detect_resident: null argument");
+	if (!h->det_on) return fail(RO_E_STATE, "detector not configured (det_w = 0)");
+	CU(cudaSetDevice(h->cfg.device));
+	cudaStream_t s = batch_stream(h);
+	int rc = launch_detect(h, s, d_rows, h->N, (long long)n_rows, d_det);
+	if (rc) return rc;
+	if (sync) CU(cudaStreamSynchronize(s));
+	return RO_OK;
+}
+
+namespace {
+
+// D2H of the configured bands (or full rows) of n rows starting at d_rows.
+int copy_rows_out(ro_wf *h, cudaStream_t s, float *dst, const float *d_rows, size_t n)
+{
+	if (!dst || n == 0) return RO_OK;
+	if (h->cfg.n_bands == 0) {
+		CU(cudaMemcpyAsync(dst, d_rows, sizeof(float) * (size_t)h->N * n, cudaMemcpyDeviceToHost, s));
+		return RO_OK;
+	}
+	size_t off = 0;
+	for (int b = 0; b < h->cfg.n_bands; b++) {
+		const size_t w = (size_t)(h->cfg.band_hi[b] - h->cfg.band_lo[b]);
+		CU(cudaMemcpy2DAsync(dst + off, sizeof(float) * (size_t)h->row_width,
+		                     d_rows + h->cfg.band_lo[b], sizeof(float) * (size_t)h->N,
+		                     sizeof(float) * w, n, cudaMemcpyDeviceToHost, s));
+		off += w;
+	}
+	return RO_OK;
+}
+
+int ensure_batch_buffers(ro_wf *h)
+{
+	if (h->d_in[0]) return RO_OK;
+	// about 256 MiB of rows per slot, at least 1 frame, at most 8192 frames
+	size_t cf = ((size_t)256 << 20) / (sizeof(float) * (size_t)h->N);
+	if (cf < 1) cf = 1;
+	if (cf > 8192) cf = 8192;
+	h->chunk_frames = cf;
+	h->d_in_bytes = ((cf - 1) * (size_t)h->hop + (size_t)h->N) * (size_t)h->in_bytes;
+	h->d_rows_bytes = cf * (size_t)h->N * sizeof(float);
+	for (int i = 0; i < 2; i++) {
+		CU(cudaMalloc(&h->d_in[i], h->d_in_bytes));
+		CU(cudaMalloc((void **)&h->d_rows[i], h->d_rows_bytes));
+		CU(cudaMalloc((void **)&h->d_det[i], sizeof(ro_det_rec) * cf));
+	}
+	return RO_OK;
+}
+
+// narrow reference `Complex` {double,double} to float32 pairs
+void narrow_complex64(float *dst, const double *src, size_t n_samples)
+{
+	for (size_t i = 0; i < 2 * n_samples; i++) dst[i] = (float)src[i];
+}
+
+}  // namespace
+
+extern "C" int ro_wf_process_host(ro_wf *h, const void *iq, size_t n_samples,
+                                  float *rows, ro_det_rec *det,
+                                  size_t max_frames, size_t *n_frames)
+{
+	if (!h || !iq) return fail(RO_E_INVALID, "ro_wf_process_host: null argument");
+	CU(cudaSetDevice(h->cfg.device));
+	size_t F = ro_wf_frame_count(h, n_samples);
+	if (F > max_frames) F = max_frames;
+	if (n_frames) *n_frames = F;
+	if (F == 0) return RO_OK;
+	int rc = ensure_batch_buffers(h);
+	if (rc) return rc;
+
+	std::vector<float> narrowed;
+	const unsigned char *src = (const unsigned char *)iq;
+	if (h->cfg.in_format == RO_IN_COMPLEX64) {
+		const size_t used = (F - 1) * (size_t)h->hop + (size_t)h->N;
+		narrowed.resize(2 * used);
+		narrow_complex64(narrowed.data(), (const double *)iq, used);
+		src = (const unsigned char *)narrowed.data();
+	}
+
+	cudaStream_t sc = batch_stream(h);
+	const size_t cf = h->chunk_frames;
+	size_t c = 0;
+	for (size_t f0 = 0; f0 < F; f0 += cf, c++) {
+		const int s = (int)(c & 1);
+		const size_t nf = std::min(cf, F - f0);
+		const size_t ns = (nf - 1) * (size_t)h->hop + (size_t)h->N;
+		// input slot is free once the kernels of chunk c-2 are done
+		if (c >= 2) CU(cudaStreamWaitEvent(h->h2d_stream, h->ev_comp[s], 0));
+		CU(cudaMemcpyAsync(h->d_in[s], src + f0 * (size_t)h->hop * (size_t)h->in_bytes,
+		                   ns * (size_t)h->in_bytes, cudaMemcpyHostToDevice, h->h2d_stream));
+		CU(cudaEventRecord(h->ev_h2d[s], h->h2d_stream));
+		CU(cudaStreamWaitEvent(sc, h->ev_h2d[s], 0));
+		// rows slot is free once the D2H of chunk c-2 is done
+		if (c >= 2) CU(cudaStreamWaitEvent(sc, h->ev_d2h[s], 0));
+		rc = launch_fft(h, sc, h->d_in[s], h->d_rows[s], h->N, (long long)nf);
+		if (rc) return rc;
+		rc = launch_detect(h, sc, h->d_rows[s], h->N, (long long)nf, det ? h->d_det[s] : NULL);
+		if (rc) return rc;
+		CU(cudaEventRecord(h->ev_comp[s], sc));
+		CU(cudaStreamWaitEvent(h->d2h_stream, h->ev_comp[s], 0));
+		rc = copy_rows_out(h, h->d2h_stream, rows ? rows + f0 * (size_t)h->row_width : NULL, h->d_rows[s], nf);
+		if (rc) return rc;
+		if (det && h->det_on)
+			CU(cudaMemcpyAsync(det + f0, h->d_det[s], sizeof(ro_det_rec) * nf, cudaMemcpyDeviceToHost, h->d2h_stream));
+		CU(cudaEventRecord(h->ev_d2h[s], h->d2h_stream));
+	}
+	CU(cudaStreamSynchronize(h->d2h_stream));
+	CU(cudaStreamSynchronize(sc));
+	CU(cudaStreamSynchronize(h->h2d_stream));
+	return RO_OK;
+}
+
+// ---------------------------------------------------------------------------
+// streaming path: Backend::process / endStream
+// ---------------------------------------------------------------------------
+namespace {
+
+int ensure_stream_buffers(ro_wf *h)
+{
+	if (h->h_stage[0]) return RO_OK;
+	const size_t N = (size_t)h->N, hop = (size_t)h->hop;
+	h->stage_cap = h->batch_frames * hop + N;
+	h->slot_rows_cap = h->stage_cap / hop + 2;
+	const size_t host_in_bytes = h->stage_cap * (size_t)h->in_bytes;
+	for (int i = 0; i < 2; i++) {
+		CU(cudaMallocHost((void **)&h->h_stage[i], host_in_bytes));
+		CU(cudaMalloc(&h->d_sin[i], (h->stage_cap + N) * (size_t)h->in_bytes));
+		CU(cudaMalloc((void **)&h->d_srows[i], h->slot_rows_cap * N * sizeof(float)));
+		CU(cudaMalloc((void **)&h->d_sdet[i], h->slot_rows_cap * sizeof(ro_det_rec)));
+		CU(cudaMallocHost((void **)&h->h_srows[i], h->slot_rows_cap * (size_t)h->row_width * sizeof(float)));
+		CU(cudaMallocHost((void **)&h->h_sdet[i], h->slot_rows_cap * sizeof(ro_det_rec)));
+	}
+	return RO_OK;
+}
+
+// wait for a batch and move its results out of the pinned slot
+int retire(ro_wf *h, Pending *p)
+{
+	if (p->slot < 0) return RO_OK;
+	CU(cudaEventSynchronize(h->ev_slot[p->slot]));
+	p->rows.assign(h->h_srows[p->slot], h->h_srows[p->slot] + p->n_rows * (size_t)h->row_width);
+	if (h->det_on) p->det.assign(h->h_sdet[p->slot], h->h_sdet[p->slot] + p->n_rows);
+	p->slot = -1;
+	return RO_OK;
+}
+
+int submit(ro_wf *h)
+{
+	const size_t total = h->carry + h->staged;
+	const size_t F = ro_wf_frame_count(h, total);
+	if (F == 0) return RO_OK;
+	const int s = h->cur;
+	cudaStream_t st = h->own_stream;
+	unsigned char *d_in = (unsigned char *)h->d_sin[s];
+	if (h->staged)
+		CU(cudaMemcpyAsync(d_in + h->carry * (size_t)h->in_bytes, h->h_stage[s],
+		                   h->staged * (size_t)h->in_bytes, cudaMemcpyHostToDevice, st));
+	int rc = launch_fft(h, st, d_in, h->d_srows[s], h->N, (long long)F);
+	if (rc) return rc;
+	rc = launch_detect(h, st, h->d_srows[s], h->N, (long long)F, h->d_sdet[s]);
+	if (rc) return rc;
+	rc = copy_rows_out(h, st, h->h_srows[s], h->d_srows[s], F);
+	if (rc) return rc;
+	if (h->det_on)
+		CU(cudaMemcpyAsync(h->h_sdet[s], h->d_sdet[s], sizeof(ro_det_rec) * F, cudaMemcpyDeviceToHost, st));
+	const size_t left = total - F * (size_t)h->hop;       // overlap carried to the next frame
+	if (left)
+		CU(cudaMemcpyAsync(h->d_sin[s ^ 1], d_in + F * (size_t)h->hop * (size_t)h->in_bytes,
+		                   left * (size_t)h->in_bytes, cudaMemcpyDeviceToDevice, st));
+	CU(cudaEventRecord(h->ev_slot[s], st));
+
+	Pending *p = new (std::nothrow) Pending();
+	if (!p) return fail(RO_E_NOMEM, "out of memory");
+	p->first_row = h->next_row;
+	p->n_rows = F;
+	p->consumed = 0;
+	p->slot = s;
+	p->done = 0;
+	h->pending.push_back(p);
+	h->next_row += F;
+	h->carry = left;
+	h->staged = 0;
+	h->cur = s ^ 1;
+	// the slot we are about to fill must be idle and its results saved
+	for (Pending *q : h->pending)
+		if (q->slot == h->cur) { rc = retire(h, q); if (rc) return rc; }
+	return RO_OK;
+}
+
+}  // namespace
+
+extern "C" int ro_wf_push(ro_wf *h, const void *iq, size_t n_samples)
+{
+	if (!h || (!iq && n_samples)) return fail(RO_E_INVALID, "ro_wf_push: null argument");
+	if (h->sticky_error) return fail(RO_E_CUDA, "handle is in a failed state");
+	CU(cudaSetDevice(h->cfg.device));
+	int rc = ensure_stream_buffers(h);
+	if (rc) { h->sticky_error = true; return rc; }
+	const size_t host_bytes = h->cfg.in_format == RO_IN_COMPLEX64 ? 16 : (size_t)h->in_bytes;
+	const unsigned char *src = (const unsigned char *)iq;
+	while (n_samples) {
+		const size_t space = h->stage_cap - h->staged;
+		const size_t take = std::min(space, n_samples);
+		unsigned char *dst = h->h_stage[h->cur] + h->staged * (size_t)h->in_bytes;
+		if (h->cfg.in_format == RO_IN_COMPLEX64) narrow_complex64((float *)dst, (const double *)src, take);
+		else memcpy(dst, src, take * host_bytes);
+		h->staged += take;
+		src += take * host_bytes;
+		n_samples -= take;
+		const size_t F = ro_wf_frame_count(h, h->carry + h->staged);
+		if (F >= h->batch_frames || h->staged == h->stage_cap) {
+			rc = submit(h);
+			if (rc) { h->sticky_error = true; return rc; }
+		}
+	}
+	return RO_OK;
+}
+
+extern "C" int ro_wf_flush(ro_wf *h)
+{
+	if (!h) return fail(RO_E_INVALID, "null handle");
+	if (h->sticky_error) return fail(RO_E_CUDA, "handle is in a failed state");
+	CU(cudaSetDevice(h->cfg.device));
+	int rc = ensure_stream_buffers(h);
+	if (rc) return rc;
+	rc = submit(h);
+	if (rc) h->sticky_error = true;
+	return rc;
+}
+
+extern "C" int ro_wf_poll(ro_wf *h, float *rows, size_t max_rows, ro_det_rec *det,
+                          size_t *n_rows, uint64_t *first_row)
+{
+	if (!h || !n_rows) return fail(RO_E_INVALID, "ro_wf_poll: null argument");
+	*n_rows = 0;
+	if (h->sticky_error) return fail(RO_E_CUDA, "handle is in a failed state");
+	CU(cudaSetDevice(h->cfg.device));
+	size_t got = 0;
+	while (got < max_rows && !h->pending.empty()) {
+		Pending *p = h->pending.front();
+		int rc = retire(h, p);
+		if (rc) { h->sticky_error = true; return rc; }
+		if (got == 0 && first_row) *first_row = p->first_row + p->consumed;
+		const size_t take = std::min(max_rows - got, p->n_rows - p->consumed);
+		if (rows)
+			memcpy(rows + got * (size_t)h->row_width, p->rows.data() + p->consumed * (size_t)h->row_width,
+			       take * (size_t)h->row_width * sizeof(float));
+		if (det && h->det_on) memcpy(det + got, p->det.data() + p->consumed, take * sizeof(ro_det_rec));
+		p->consumed += take;
+		got += take;
+		if (p->consumed == p->n_rows) { h->pending.pop_front(); delete p; }
+	}
+	*n_rows = got;
+	return RO_OK;
+}
+
+extern "C" int ro_wf_reset(ro_wf *h)
+{
+	if (!h) return fail(RO_E_INVALID, "null handle");
+	CU(cudaSetDevice(h->cfg.device));
+	CU(cudaStreamSynchronize(h->own_stream));
+	for (Pending *p : h->pending) delete p;
+	h->pending.clear();
+	h->carry = h->staged = 0;
+	h->next_row = 0;
+	h->cur = 0;
+	h->sticky_error = false;
+	return RO_OK;
+}
