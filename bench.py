@@ -317,7 +317,11 @@ def main():
     d_iq = gen_iq_device(torch, S, 0x5EED0002 + rank, dev)
     d_rows = torch.empty(F * BINS, dtype=torch.float32, device=dev)
     d_det = torch.empty(F * 4, dtype=torch.int32, device=dev)
-    stream = torch.cuda.current_stream()
+    # a dedicated non-default stream: the default stream's handle is 0, which the C ABI
+    # reads as "use the handle's own stream" and torch events would then time nothing
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
     wf.set_stream(stream.cuda_stream)
 
     def step_resident():
