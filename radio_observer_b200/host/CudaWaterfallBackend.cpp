@@ -1,0 +1,206 @@
+/*
+ * CudaWaterfallBackend.cpp -- see CudaWaterfallBackend.h.
+ *
+ * What stays on the host, restated from FFTBackend::process
+ * (reference src/FFTBackend.cpp:192-279) because the recorders depend on it:
+ *   - every incoming sample is pushed to the raw I/Q ring (rawBuffer_) and gets a
+ *     RawDataHandle {ring mark, stream time}            (:217-223, :264-270)
+ *   - a frame is complete when the window holds bins_ samples; its row time is the
+ *     handle time of the window's first sample            (:225)
+ *   - the handle table is shifted by the hop BEFORE processFFT is called, so the
+ *     rawMark handed over is the one of the NEXT frame's first sample whenever
+ *     overlap > 0                                           (:241-251)
+ * What moves to the GPU: IQ gain, window, FFT, magnitude.  A finished row comes
+ * back as bins_ fftshifted floats; it is handed to the unmodified
+ * WaterfallBackend::processFFT as the complex vector (row[(i+N/2)%N], 0), whose
+ * magnitude sqrt(x*x + 0) is exactly x in double, so the ring receives the GPU
+ * row bit for bit and every recorder runs as in the reference.
+ */
+#include "CudaWaterfallBackend.h"
+
+#include <cstring>
+
+CudaWaterfallBackend::CudaWaterfallBackend(int bins, int overlap, std::string origin,
+                                           int device, int batchFrames) :
+	WaterfallBackend(bins, overlap, origin),
+	overlap_(overlap),
+	device_(device),
+	batchFrames_(batchFrames < 1 ? 1 : batchFrames),
+	iqGain_(0), iqPhaseShift_(0),
+	wf_(NULL), failed_(false),
+	fill_(0),
+	delivered_(0)
+{
+	if (overlap_ < 0) overlap_ = 0;
+	if (overlap_ >= bins_) overlap_ = bins_ - 1;
+}
+
+
+CudaWaterfallBackend::~CudaWaterfallBackend()
+{
+	if (wf_) ro_wf_destroy(wf_);
+	wf_ = NULL;
+}
+
+
+void CudaWaterfallBackend::fail(const char *what)
+{
+	// the reference's convention on the data path: log and stop producing
+	LOG_ERROR("CudaWaterfallBackend: " << what << ": " << ro_last_error());
+	failed_ = true;
+}
+
+
+void CudaWaterfallBackend::startStream(StreamInfo info)
+{
+	// sizes the row ring and the raw ring, starts the recorders, sets
+	// fftSampleRate_ (src/WaterfallBackend.cpp:573-594, src/FFTBackend.cpp:144-189)
+	WaterfallBackend::startStream(info);
+
+	fill_ = 0;
+	info_ = DataInfo();
+	pending_.clear();
+	windowRaw_.assign(bins_, RawDataHandle());
+	{
+		int cap = (1 << 22) / bins_;          // about 16 MiB of harvested rows at a time
+		if (cap < 1) cap = 1;
+		if (cap > 64) cap = 64;
+		rows_.resize((size_t)bins_ * cap);
+	}
+	asComplex_.assign(2 * (size_t)bins_, 0.0);
+	delivered_ = 0;
+	failed_ = false;
+
+	if (wf_) { ro_wf_destroy(wf_); wf_ = NULL; }
+	ro_wf_config cfg;
+	memset(&cfg, 0, sizeof cfg);
+	cfg.bins = bins_;
+	cfg.overlap = overlap_;
+	cfg.sample_rate = info.sampleRate;
+	cfg.in_format = RO_IN_COMPLEX64;          // the Pipeline hands over vector<Complex>
+	cfg.iq_gain = getGain();
+	cfg.iq_phase_shift = getPhaseShift();
+	cfg.n_bands = 0;                          // recorders slice the full row themselves
+	cfg.device = device_;
+	cfg.max_batch_frames = batchFrames_;
+	if (ro_wf_create(&cfg, &wf_) != RO_OK) {
+		wf_ = NULL;
+		fail("ro_wf_create");
+	}
+}
+
+
+void CudaWaterfallBackend::pushSamples(const Complex *src, int count, WFTime timeOffset)
+{
+	for (int i = 0; i < count; i++) {
+		floatToInt(src[i], rawBuffer_.push());
+		windowRaw_[fill_ + i] = RawDataHandle(
+			rawBuffer_.mark(),
+			timeOffset.addSamples(i, streamInfo_.sampleRate)
+		);
+	}
+	if (ro_wf_push(wf_, src, (size_t)count) != RO_OK) fail("ro_wf_push");
+}
+
+
+void CudaWaterfallBackend::process(const std::vector<Complex> &data, DataInfo info)
+{
+	if (failed_ || !wf_ || data.empty()) return;
+
+	int size = data.size();
+	const Complex *src = &(data[0]);
+	WFTime timeOffset = info.timeOffset;
+
+	while (size >= (bins_ - fill_)) {
+		int count = bins_ - fill_;
+		pushSamples(src, count, timeOffset);
+		if (failed_) return;
+
+		info_.timeOffset = windowRaw_[0].time;
+
+		const int hop = bins_ - overlap_;
+		memmove(&windowRaw_[0], &windowRaw_[0] + hop, overlap_ * sizeof(windowRaw_[0]));
+		fill_ = overlap_;
+		size -= count;
+		src += count;
+
+		PendingFrame p;
+		p.info = info_;
+		p.rawMark = windowRaw_[0].mark;
+		pending_.push_back(p);
+
+		timeOffset = timeOffset.addSamples(count, streamInfo_.sampleRate);
+		info_.offset++;
+
+		if ((int)pending_.size() >= batchFrames_) harvest(true);
+		if (failed_) return;
+	}
+
+	if (size > 0) {
+		pushSamples(src, size, timeOffset);
+		fill_ += size;
+	}
+}
+
+
+void CudaWaterfallBackend::harvest(bool flush)
+{
+	if (flush && ro_wf_flush(wf_) != RO_OK) { fail("ro_wf_flush"); return; }
+	const int half = bins_ / 2;
+	const size_t cap = rows_.size() / (size_t)bins_;
+	while (!pending_.empty()) {
+		size_t n = 0;
+		uint64_t first = 0;
+		if (ro_wf_poll(wf_, &rows_[0], cap, NULL, &n, &first) != RO_OK) { fail("ro_wf_poll"); return; }
+		if (n == 0) break;
+		for (size_t r = 0; r < n && !pending_.empty(); r++) {
+			const float *row = &rows_[r * (size_t)bins_];
+			// undo the fftshift: processFFT writes data[i] to row[(i + half) % bins_]
+			for (int i = 0; i < half; i++) asComplex_[2 * i] = row[half + i];
+			for (int i = half; i < bins_; i++) asComplex_[2 * i] = row[i - half];
+			PendingFrame p = pending_.front();
+			pending_.pop_front();
+			WaterfallBackend::processFFT((const fftw_complex *)&asComplex_[0], bins_, p.info, p.rawMark);
+			delivered_++;
+		}
+	}
+}
+
+
+void CudaWaterfallBackend::endStream()
+{
+	// complete frames still in flight are delivered; the incomplete tail is dropped
+	// exactly as the reference never flushes window_ (src/FFTBackend.cpp:282-286)
+	if (wf_ && !failed_) harvest(true);
+	WaterfallBackend::endStream();
+	if (wf_) { ro_wf_destroy(wf_); wf_ = NULL; }
+}
+
+
+Ref<DIObject> CudaWaterfallBackend::make(Ref<DynObject> config, Ref<DIObject> parent)
+{
+	// the keys of WaterfallBackend::make (src/WaterfallBackend.cpp:620-644) with
+	// the same defaults, plus cuda_device / cuda_batch_frames
+	int bins      = config->getStrInt("bins",        32768);
+	int overlap   = config->getStrInt("overlap",         0);
+	string origin = config->getStrString("origin", "debug");
+
+	Ref<CudaWaterfallBackend> backend = new CudaWaterfallBackend(
+		bins, overlap, origin,
+		config->getStrInt("cuda_device", 0),
+		config->getStrInt("cuda_batch_frames", 1)
+	);
+
+	backend->setMetadataPath(
+		config->getStrString("metadata_path", "."));
+	backend->setBufferChunkSize(
+		config->getStrInt("buffer_chunk_size", WATERFALL_BACKEND_CHUNK_SIZE));
+	backend->setGain(
+		config->getStrDouble("iq_gain", 0));
+	backend->setPhaseShift(
+		config->getStrInt("iq_phase_shift", 0));
+
+	return backend;
+}
+
+CPPAPP_DI_METHOD("waterfall_cuda", CudaWaterfallBackend, make);
