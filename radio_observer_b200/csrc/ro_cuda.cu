@@ -17,6 +17,7 @@
 
 #include "../../include/ro_cuda.h"
 #include "ro_kernels.cuh"
+#include "ro_v2.h"
 
 namespace {
 
@@ -99,6 +100,10 @@ struct ro_wf {
 	KernelChoice kc;
 	int grid_cap;                         // resident CTAs for the persistent grid
 	det_kernel_t det_fn;
+	// v2 kernels (int16 input, N = 4096..16384, symmetric window): [0] direct loads, [1] TMA-staged ring
+	bool v2_ok;
+	ro::V2Kernel v2[2];
+	int v2_grid_cap[2];
 
 	float  *d_window;
 	float2 *d_tw;
@@ -279,6 +284,28 @@ int launch_fft(ro_wf *h, cudaStream_t s, const void *d_iq, float *d_rows, long l
                long long n_frames)
 {
 	if (n_frames <= 0) return RO_OK;
+	// v2 stores 2 or 4 adjacent magnitudes with one vector store: rows must be 16-byte aligned
+	if (h->v2_ok && ((uintptr_t)d_rows & 15) == 0 && (row_stride & 3) == 0) {
+		// the staged variant needs 16-byte aligned frame starts for cp.async.bulk
+		const int st = (h->hop % 4 == 0 && ((uintptr_t)d_iq & 15) == 0) ? 1 : 0;
+		const long long cap = h->v2_grid_cap[st];
+		const long long fpc = (n_frames + cap - 1) / cap;          // contiguous frames per CTA
+		const int grid = (int)((n_frames + fpc - 1) / fpc);
+		cudaEvent_t e0 = 0, e1 = 0;
+		if (h->profiling) {
+			int rc = get_event(h, &e0); if (rc) return rc;
+			rc = get_event(h, &e1); if (rc) return rc;
+			CU(cudaEventRecord(e0, s));
+		}
+		CU(ro::v2_launch(h->v2[st], grid, s, d_iq, h->d_window, h->d_tw, d_rows, row_stride, n_frames,
+		                 h->hop, fpc, (float)h->cfg.iq_gain));
+		h->launches++;
+		if (h->profiling) {
+			CU(cudaEventRecord(e1, s));
+			h->ev_used[0].push_back(std::make_pair(e0, e1));
+		}
+		return RO_OK;
+	}
 	ro::WfParams p;
 	p.iq = d_iq;
 	p.window = h->d_window;
@@ -453,6 +480,24 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 	CUH(cudaMalloc(&h->d_tw, sizeof(float2) * N));
 	CUH(cudaMemcpy(h->d_window, win.data(), sizeof(float) * N, cudaMemcpyHostToDevice));
 	CUH(cudaMemcpy(h->d_tw, tw.data(), sizeof(float2) * N, cudaMemcpyHostToDevice));
+	{   // v2 eligibility: int16 input, an instantiated size, and w[i] == w[N-1-i] bit for bit
+		bool sym = true;
+		for (int i = 0; i < N / 2 && sym; i++) sym = memcmp(&win[i], &win[N - 1 - i], sizeof(float)) == 0;
+		const bool gain = cfg->iq_gain != 0.0;
+		h->v2_ok = false;
+		const char *force_v1 = getenv("RO_FORCE_V1");
+		if (sym && h->fmt == ro::FMT_INT16 && !(force_v1 && force_v1[0] == '1') &&
+		    ro::v2_pick(h->log2n, false, gain, &h->v2[0]) && ro::v2_pick(h->log2n, true, gain, &h->v2[1])) {
+			h->v2_ok = true;
+			for (int st = 0; st < 2; st++) {
+				CUH(cudaFuncSetAttribute(h->v2[st].fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->v2[st].smem));
+				int occ2 = 0;
+				CUH(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, h->v2[st].fn, h->v2[st].threads, h->v2[st].smem));
+				if (occ2 < 1) { h->v2_ok = false; break; }
+				h->v2_grid_cap[st] = occ2 * h->n_sms;
+			}
+		}
+	}
 	CUH(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
 	CUH(cudaStreamCreateWithFlags(&h->h2d_stream, cudaStreamNonBlocking));
 	CUH(cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking));

@@ -1,0 +1,127 @@
+// ro_fft2.cuh -- packed-FP32 (f32x2) radix-2^k FFT building blocks for sm_100a.
+//
+// Blackwell's FMA pipe executes add/mul/fma.f32x2 on a 64-bit register pair:
+// one issue slot, two lanes.  A complex number is kept as one packed pair
+// (re in the low lane, im in the high lane), so a complex add is ONE FADD2 and
+// a complex multiply is FMUL2 + FFMA2; ptxas folds the lane swap, the per-lane
+// sign and scalar broadcasts into operand modifiers (.LO_HI, .NP, .F32), so no
+// data-movement instruction is emitted (checked with cuobjdump: a 32-point
+// transform is 130 FADD2 + 64 FFMA2 + 34 FMUL2 = 228 instructions against 456
+// scalar ones).  Measured on B200 (profiles/r01_microbench_pipe_rates.txt):
+// packed ops issue at 2.0 warp-instr/clk/SM = the full 128 lanes/clk, whereas
+// three-register scalar FFMA reaches only 2.6.
+//
+// Same transform as ro_fft.cuh (reference: fftw_execute, src/FFTBackend.cpp:236).
+#pragma once
+#include <cuda_runtime.h>
+#include "ro_fft.cuh"
+
+namespace ro {
+
+typedef unsigned long long c64;   // packed complex: {re (low 32 bits), im (high 32 bits)}
+
+__device__ __forceinline__ c64 pk(float lo, float hi)
+{
+	c64 r;
+	asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi));
+	return r;
+}
+__device__ __forceinline__ void upk(c64 v, float &lo, float &hi)
+{
+	asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ c64 swp(c64 v) { float a, b; upk(v, a, b); return pk(b, a); }
+__device__ __forceinline__ c64 add2(c64 a, c64 b) { c64 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ c64 sub2(c64 a, c64 b) { c64 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ c64 mul2(c64 a, c64 b) { c64 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ c64 fma2(c64 a, c64 b, c64 c) { c64 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+
+// z * (wr + i*wi):  (zr*wr - zi*wi, zi*wr + zr*wi)
+__device__ __forceinline__ c64 cmul2(c64 z, float wr, float wi)
+{
+	return fma2(swp(z), pk(-wi, wi), mul2(z, pk(wr, wr)));
+}
+__device__ __forceinline__ c64 cmul2(c64 z, c64 w)
+{
+	float wr, wi;
+	upk(w, wr, wi);
+	return cmul2(z, wr, wi);
+}
+
+// In-place forward DIF FFT of R packed points; output k is left at v[bitrev(k)].
+template <int R>
+__device__ __forceinline__ void fft_dif2(c64 (&v)[R])
+{
+	static_assert(R >= 2 && R <= 32 && (R & (R - 1)) == 0, "radix");
+	constexpr int L = ilog2(R);
+#pragma unroll
+	for (int lvl = 0; lvl < L; lvl++) {
+		const int half = R >> (lvl + 1);
+#pragma unroll
+		for (int s = 0; s < R; s += 2 * half) {
+#pragma unroll
+			for (int j = 0; j < half; j++) {
+				const c64 a = v[s + j], b = v[s + j + half];
+				const int e = j * (16 / half);            // W_{2*half}^j = W_32^e
+				v[s + j] = add2(a, b);
+				const c64 d = sub2(a, b);
+				if (e == 0) v[s + j + half] = d;
+				else if (e == 8) v[s + j + half] = mul2(swp(d), pk(1.f, -1.f));   // * (-i); folded by ptxas
+				else v[s + j + half] = cmul2(d, cw32(e), -sw32(e));
+			}
+		}
+	}
+}
+
+// Multiply output k (at v[bitrev(k)]) by w^k, k = 1..R-1; base[i] = w^(2^i)
+// read from the once-rounded table.  Same composition as twiddle_powers().
+template <int R>
+__device__ __forceinline__ void twiddle_powers2(c64 (&v)[R], const c64 (&base)[ilog2(R)])
+{
+	constexpr int L = ilog2(R);
+	constexpr int LB = (L + 1) / 2;
+	constexpr int NLO = 1 << LB;
+	constexpr int NHI = 1 << (L - LB);
+	c64 lo[NLO];
+	lo[0] = pk(1.f, 0.f);
+#pragma unroll
+	for (int msb = 0; msb < LB; msb++) {
+		lo[1 << msb] = base[msb];
+#pragma unroll
+		for (int rest = 1; rest < (1 << msb); rest++)
+			lo[(1 << msb) + rest] = cmul2(lo[rest], base[msb]);
+	}
+	c64 hi[NHI];
+	hi[0] = pk(1.f, 0.f);
+#pragma unroll
+	for (int msb = 0; msb < L - LB; msb++) {
+		hi[1 << msb] = base[LB + msb];
+#pragma unroll
+		for (int rest = 1; rest < (1 << msb); rest++)
+			hi[(1 << msb) + rest] = cmul2(hi[rest], base[LB + msb]);
+	}
+#pragma unroll
+	for (int h = 0; h < NHI; h++) {
+#pragma unroll
+		for (int j = 0; j < NLO; j++) {
+			const int k = h * NLO + j;
+			if (k == 0) continue;
+			const c64 w = h == 0 ? lo[j] : (j == 0 ? hi[h] : cmul2(lo[j], hi[h]));
+			v[bitrev(k, L)] = cmul2(v[bitrev(k, L)], w);
+		}
+	}
+}
+
+// ---- int16 I/Q -> packed float without the XU pipe --------------------------
+// cvt.rn.f32.s16 runs on the 16-lane XU pipe (measured 0.5 warp-instr/clk/SM).
+// Instead: flip the sign bits (x + 32768 as unsigned), splice the 16 bits into
+// the mantissa of 2^23 with PRMT, subtract 2^23 + 32768: exact, ALU + FMA pipes.
+__device__ __forceinline__ c64 short2_to_c64(unsigned int v)
+{
+	const unsigned int u = v ^ 0x80008000u;
+	const float re = __uint_as_float(__byte_perm(u, 0x4b000000u, 0x7410));
+	const float im = __uint_as_float(__byte_perm(u, 0x4b000000u, 0x7432));
+	return add2(pk(re, im), pk(-8421376.0f, -8421376.0f));
+}
+
+}  // namespace ro
