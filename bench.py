@@ -376,11 +376,13 @@ def main():
             traffic = None
     flops = 5.0 * BINS * math.log2(BINS) * F
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "kernel": "wf_fft_kernel<14,32,16,int16>", "kernel_ms": fft_ms,
+                "traffic": traffic, "kernel": "wf_fft2_kernel<14,32,16,STAGE> (packed f32x2, TMA-staged ring)", "kernel_ms": fft_ms,
                 "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
                 "fft_tflops_5NlogN": flops / (fft_ms * 1e-3) / 1e12,
                 "detector_kernel_ms": kms[1] / max(1, kn[1]),
-                "note": "75% overlap: 280 flop/sample puts this shape past the FP32 ridge; the binding roof is FP32 issue + shared memory, see DESIGN.md"}
+                "fp32_roof": {"lane_ops_per_frame": 1877 * 512, "fma_pipe_floor_cycles_per_frame": 7508,
+                              "note": "FMA-pipe floor (128 lanes/clk/SM, profiles/r01_microbench_pipe_rates.txt) = 38.8 M frames/s = 0.485 of HBM peak at 20 B/sample"},
+                "note": "75% overlap: 280 flop/sample puts this shape past the FP32 ridge; the binding roof is the FMA pipe, not HBM; see DESIGN.md section 4"}
 
     # ---- end to end through the host API: pinned host in, bands + detector records out ----
     h_iq = PinnedArray((2 * S,), np.int16)
