@@ -104,6 +104,15 @@ struct ro_wf {
 	bool v2_ok;
 	ro::V2Kernel v2[2];
 	int v2_grid_cap[2];
+	// frames longer than 16384 points: wf_split_kernel (first radix-Na step, once per frame) into a
+	// cache-sized scratch, then wf_fft2_kernel<MODE_SPLIT> per residue class
+	bool split_ok;
+	ro::V2Kernel v2s;
+	int v2s_grid_cap;
+	int log2na;
+	float2 *d_tw_nb;                      // exp(-2*pi*i*j/16384)
+	void   *d_scratch;                    // [scratch_frames][N] packed complex float
+	long long scratch_frames;
 
 	float  *d_window;
 	float2 *d_tw;
@@ -284,6 +293,33 @@ int launch_fft(ro_wf *h, cudaStream_t s, const void *d_iq, float *d_rows, long l
                long long n_frames)
 {
 	if (n_frames <= 0) return RO_OK;
+	if (h->split_ok) {
+		cudaEvent_t e0 = 0, e1 = 0;
+		if (h->profiling) {
+			int rc = get_event(h, &e0); if (rc) return rc;
+			rc = get_event(h, &e1); if (rc) return rc;
+			CU(cudaEventRecord(e0, s));
+		}
+		for (long long f0 = 0; f0 < n_frames; f0 += h->scratch_frames) {
+			const long long nf = std::min<long long>(h->scratch_frames, n_frames - f0);
+			CU(ro::v2_launch_split(s, h->log2n, h->log2na, h->fmt == ro::FMT_FLOAT32, d_iq, h->d_window, h->d_tw,
+			                       h->d_scratch, f0, nf, h->hop, (float)h->cfg.iq_gain));
+			const long long items = nf << h->log2na;
+			const long long cap = h->v2s_grid_cap;
+			long long ipc = (items + cap - 1) / cap;                 // contiguous items per CTA
+			const int pair = (((uintptr_t)d_rows & 15) == 0 && (row_stride & 3) == 0 && !getenv("RO_SPLIT_NOPAIR")) ? 1 : 0;
+			if (pair) ipc += ipc & 1;                                // classes r, r+1 stay in one CTA
+			const int grid = (int)((items + ipc - 1) / ipc);
+			CU(ro::v2_launch(h->v2s, grid, s, h->d_scratch, NULL, h->d_tw_nb, d_rows + f0 * row_stride, row_stride,
+			                 items, 0, ipc, 0.f, h->log2na, pair));
+			h->launches += 2;
+		}
+		if (h->profiling) {
+			CU(cudaEventRecord(e1, s));
+			h->ev_used[0].push_back(std::make_pair(e0, e1));
+		}
+		return RO_OK;
+	}
 	// v2 stores 2 or 4 adjacent magnitudes with one vector store: rows must be 16-byte aligned
 	if (h->v2_ok && ((uintptr_t)d_rows & 15) == 0 && (row_stride & 3) == 0) {
 		// the staged variant needs 16-byte aligned frame starts for cp.async.bulk
@@ -298,7 +334,7 @@ int launch_fft(ro_wf *h, cudaStream_t s, const void *d_iq, float *d_rows, long l
 			CU(cudaEventRecord(e0, s));
 		}
 		CU(ro::v2_launch(h->v2[st], grid, s, d_iq, h->d_window, h->d_tw, d_rows, row_stride, n_frames,
-		                 h->hop, fpc, (float)h->cfg.iq_gain));
+		                 h->hop, fpc, (float)h->cfg.iq_gain, 0, 0));
 		h->launches++;
 		if (h->profiling) {
 			CU(cudaEventRecord(e1, s));
@@ -391,6 +427,8 @@ void free_all(ro_wf *h)
 	for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
 	cudaFree(h->d_window);
 	cudaFree(h->d_tw);
+	cudaFree(h->d_tw_nb);
+	cudaFree(h->d_scratch);
 	if (h->own_stream) cudaStreamDestroy(h->own_stream);
 	if (h->h2d_stream) cudaStreamDestroy(h->h2d_stream);
 	if (h->d2h_stream) cudaStreamDestroy(h->d2h_stream);
@@ -487,7 +525,7 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 		h->v2_ok = false;
 		const char *force_v1 = getenv("RO_FORCE_V1");
 		if (sym && h->fmt == ro::FMT_INT16 && !(force_v1 && force_v1[0] == '1') &&
-		    ro::v2_pick(h->log2n, false, gain, &h->v2[0]) && ro::v2_pick(h->log2n, true, gain, &h->v2[1])) {
+		    ro::v2_pick(h->log2n, ro::V2_DIRECT, gain, &h->v2[0]) && ro::v2_pick(h->log2n, ro::V2_STAGED, gain, &h->v2[1])) {
 			h->v2_ok = true;
 			for (int st = 0; st < 2; st++) {
 				CUH(cudaFuncSetAttribute(h->v2[st].fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->v2[st].smem));
@@ -496,6 +534,41 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 				if (occ2 < 1) { h->v2_ok = false; break; }
 				h->v2_grid_cap[st] = occ2 * h->n_sms;
 			}
+		}
+	}
+	h->split_ok = false;
+	int log2nb = 14;                              // in-CTA transform of the split path
+	if (const char *e3 = getenv("RO_SPLIT_LOG2NB")) log2nb = atoi(e3);
+	if (h->log2n - log2nb > 5) log2nb = h->log2n - 5;      // the split kernel does radix <= 32
+	if (h->log2n > 14 && !(getenv("RO_FORCE_V1") && getenv("RO_FORCE_V1")[0] == '1') &&
+	    ro::v2_pick(log2nb, ro::V2_SPLIT, false, &h->v2s)) {
+		h->log2na = h->log2n - log2nb;
+		const int NBv = 1 << log2nb;
+		CUH(cudaFuncSetAttribute(h->v2s.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->v2s.smem));
+		int occ3 = 0;
+		CUH(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ3, h->v2s.fn, h->v2s.threads, h->v2s.smem));
+		if (occ3 >= 1) {
+			h->v2s_grid_cap = occ3 * h->n_sms;
+			std::vector<float> twb(2 * (size_t)NBv);
+			ro_twiddle_table(NBv, twb.data());
+			CUH(cudaMalloc(&h->d_tw_nb, sizeof(float2) * NBv));
+			CUH(cudaMemcpy(h->d_tw_nb, twb.data(), sizeof(float2) * NBv, cudaMemcpyHostToDevice));
+			// a batch = whole waves of the persistent grid.  Measured on B200 (32k/64k frames): a 40 MB
+			// scratch that stays in the 126 MB L2 gives only 2 items per CTA per launch and loses more to
+			// launch gaps and tails than a 256 MB scratch loses to HBM (3.9 vs 4.5 M frames/s at 32k);
+			// RO_SCRATCH_MB overrides
+			const long long na = 1LL << h->log2na;
+			long long unit = h->v2s_grid_cap, a = unit, b = na;     // frames per wave = cap / gcd(cap, Na)
+			while (b) { long long t2 = a % b; a = b; b = t2; }
+			unit /= a;
+			long long budget_mb = 256;
+			if (const char *e2 = getenv("RO_SCRATCH_MB")) budget_mb = atoll(e2) > 0 ? atoll(e2) : budget_mb;
+			const long long frame_bytes = 8LL * N;
+			long long units = (budget_mb << 20) / (unit * frame_bytes);
+			if (units < 1) units = 1;
+			h->scratch_frames = units * unit;
+			CUH(cudaMalloc(&h->d_scratch, (size_t)(h->scratch_frames * frame_bytes)));
+			h->split_ok = true;
 		}
 	}
 	CUH(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));

@@ -36,7 +36,16 @@ struct Wf2Params {
 	long long     row_stride;
 	long long     frames_per_cta;
 	float         iq_gain;
+	int           log2na;       // MODE_SPLIT: the frame has Na = 2^log2na residue classes of N points each
+	int           pair;         // MODE_SPLIT: rows are 16-byte aligned and every CTA starts on an even item:
+	                            // classes r, r+1 are stored together (see the store stage)
 };
+
+// where the N points of one item come from / where its magnitudes go
+enum { MODE_DIRECT = 0,   // int16 I/Q read from global memory, row = item
+       MODE_STAGED = 1,   // int16 I/Q through the TMA-staged shared-memory ring, row = item
+       MODE_SPLIT  = 2 }; // packed complex float from wf_split_kernel (already windowed, first
+                          // radix-Na step done): item = frame*Na + r, output k is bin Na*k + r
 
 __device__ __forceinline__ unsigned int smem_u32(const void *p)
 {
@@ -74,18 +83,22 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned in
 }
 
 // bytes of dynamic shared memory the kernel needs
-template <int LOG2N, int P, int R3, bool STAGE>
+template <int LOG2N, int P, int R3, int MODE>
 constexpr size_t wf2_smem_bytes()
 {
 	constexpr size_t N = (size_t)1 << LOG2N;
 	constexpr size_t PAD1 = (R3 < 16) ? R3 : 0;
-	return sizeof(c64) * (N + P * PAD1) + sizeof(float) * (N / 2) + 32 + (STAGE ? 4 * N : 0);
+	return sizeof(c64) * (N + P * PAD1) + (MODE == MODE_SPLIT ? 0 : sizeof(float) * (N / 2)) + 32 +
+	       (MODE == MODE_STAGED ? 4 * N : 0) + (MODE == MODE_SPLIT && P / R3 >= 2 ? 4 * N : 0);
 }
 
-template <int LOG2N, int P, int R3, bool STAGE, bool GAIN, int MINB>
+template <int LOG2N, int P, int R3, int MODE, bool GAIN, int MINB>
 __global__ void __launch_bounds__((1 << LOG2N) / P, MINB)
 wf_fft2_kernel(const Wf2Params p)
 {
+	constexpr bool STAGE = MODE == MODE_STAGED;
+	constexpr bool SPLIT = MODE == MODE_SPLIT;
+	constexpr int WINF = SPLIT ? 0 : (1 << LOG2N) / 2;      // floats of window table in shared memory
 	constexpr int N = 1 << LOG2N;
 	constexpr int R1 = P, R2 = P;
 	constexpr int T = N / P;
@@ -104,7 +117,7 @@ wf_fft2_kernel(const Wf2Params p)
 	c64 *S = reinterpret_cast<c64 *>(smem_raw);
 	float *win = reinterpret_cast<float *>(S + N + P * PAD1);
 	// [0] TMA completion, [1] "pass-2 inputs read", [2] "pass-3 inputs read" (split barriers)
-	unsigned long long *mbar = reinterpret_cast<unsigned long long *>(win + N / 2);
+	unsigned long long *mbar = reinterpret_cast<unsigned long long *>(win + WINF);
 	unsigned long long *bar_rd2 = mbar + 1, *bar_rd3 = mbar + 2;
 	unsigned int *ring = reinterpret_cast<unsigned int *>(mbar + 4);
 
@@ -122,7 +135,7 @@ wf_fft2_kernel(const Wf2Params p)
 		mbar_init(bar_rd2, T);
 		mbar_init(bar_rd3, T);
 	}
-	for (int i = t; i < N / 2; i += T) win[i] = __ldg(p.window_half + i);
+	for (int i = t; i < WINF; i += T) win[i] = __ldg(p.window_half + i);
 	__syncthreads();
 	if (STAGE && t == 0) {
 		mbar_expect_tx(mbar, 4u * N);
@@ -161,6 +174,10 @@ wf_fft2_kernel(const Wf2Params p)
 				const float w = (n1 < R1 / 2) ? win[n1 * M + t] : win[(R1 - 1 - n1) * M + (M - 1 - t)];
 				v[n1] = mul2(GAIN ? add2(x, gain2) : x, pk(w, w));
 			}
+		} else if (SPLIT) {
+			const unsigned long long *src = reinterpret_cast<const unsigned long long *>(p.iq) + f * N;
+#pragma unroll
+			for (int n1 = 0; n1 < R1; n1++) v[n1] = __ldg(src + n1 * M + t);
 		} else {
 			const unsigned int *src = reinterpret_cast<const unsigned int *>(p.iq) + f * hop;
 #pragma unroll
@@ -252,6 +269,52 @@ wf_fft2_kernel(const Wf2Params p)
 					mag[k3][c] = fast_sqrt(fmaf(zr, zr, zi * zi));
 				}
 			}
+			if (SPLIT) {
+				// output k of residue class r is bin Na*k + r of the Na*N-point frame
+				const int la = p.log2na;
+				const int r = (int)(f & ((1 << la) - 1));
+				float *row = p.rows + (f >> la) * p.row_stride;
+				const int big_mask = (N << la) - 1, big_half = (N << la) >> 1;
+				if (p.pair) {
+					// Alone, a class writes 4 bytes of every 4*Na: 32 scattered stores per thread and a
+					// queue of partial sectors (lg_throttle was the top stall).  Instead an even class
+					// parks its magnitudes in a thread-private slice of shared memory, and the odd class
+					// that the same thread transforms next stores both: bins Na*k + r - 1, Na*k + r.
+					float *stash = reinterpret_cast<float *>(mbar + 4);
+					if ((r & 1) == 0) {
+#pragma unroll
+						for (int k3 = 0; k3 < R3; k3++)
+#pragma unroll
+							for (int c = 0; c < G; c++) stash[(k3 * G + c) * T + t] = mag[k3][c];
+					} else {
+#pragma unroll
+						for (int k3 = 0; k3 < R3; k3++) {
+							float ev[G];
+#pragma unroll
+							for (int c = 0; c < G; c++) ev[c] = stash[(k3 * G + c) * T + t];
+							const int k = k3 * (N / R3) + G * t;
+							if (G == 2 && la == 1) {
+								*reinterpret_cast<float4 *>(row + (((k << 1) + big_half) & big_mask)) =
+									make_float4(ev[0], mag[k3][0], ev[1], mag[k3][1]);
+							} else {
+#pragma unroll
+								for (int c = 0; c < G; c++)
+									*reinterpret_cast<float2 *>(row + ((((k + c) << la) + r - 1 + big_half) & big_mask)) =
+										make_float2(ev[c], mag[k3][c]);
+							}
+						}
+					}
+				} else {
+#pragma unroll
+				for (int k3 = 0; k3 < R3; k3++) {
+#pragma unroll
+					for (int c = 0; c < G; c++) {
+						const int k = k3 * (N / R3) + G * t + c;
+						row[((k << la) + r + big_half) & big_mask] = mag[k3][c];
+					}
+				}
+				}
+			} else {
 			float *row = p.rows + f * p.row_stride + G * t;
 #pragma unroll
 			for (int k3 = 0; k3 < R3; k3++) {
@@ -260,8 +323,12 @@ wf_fft2_kernel(const Wf2Params p)
 				if (G == 2) *reinterpret_cast<float2 *>(row + off) = make_float2(mag[k3][0], mag[k3][1]);
 				else *reinterpret_cast<float4 *>(row + off) = make_float4(mag[k3][0], mag[k3][1], mag[k3][2 % G], mag[k3][3 % G]);
 			}
+			}
 		} else {
-			float *row = p.rows + f * p.row_stride + t;
+			const int la = SPLIT ? p.log2na : 0;
+			const int big_mask = (N << la) - 1, big_half = (N << la) >> 1;
+			float *row = SPLIT ? p.rows + (f >> la) * p.row_stride + (int)(f & ((1 << la) - 1))
+			                   : p.rows + f * p.row_stride + t;
 			c64 u[R3];
 #pragma unroll
 			for (int n3 = 0; n3 < R3; n3++) u[n3] = S[((t / R1) * R3 + n3) * R1 + ((t % R1) ^ (n3 * SW))];
@@ -272,10 +339,64 @@ wf_fft2_kernel(const Wf2Params p)
 				const int off = (k3 * (N / R3) + N / 2) & NMASK;   // t < N/R3 = T
 				float zr, zi;
 				upk(u[bitrev(k3, L3)], zr, zi);
-				row[off] = fast_sqrt(fmaf(zr, zr, zi * zi));
+				if (SPLIT) row[(((k3 * (N / R3) + t) << la) + big_half) & big_mask] = fast_sqrt(fmaf(zr, zr, zi * zi));
+				else row[off] = fast_sqrt(fmaf(zr, zr, zi * zi));
 			}
 		}
 	}
+}
+
+// ---------------------------------------------------------------------------
+// Frames longer than the in-CTA transform (N = Na*Nb, Nb = 16384): the first
+// radix-Na decimation-in-frequency step, done ONCE per frame for all Na residue
+// classes (v1 redid it in every class's CTA):
+//     y_r[m] = W_N^{m*r} * sum_q xw[q*Nb + m] * W_Na^{q*r},   X[Na*k + r] = DFT_Nb(y_r)[k]
+// with xw = (sample + i*gain) * window  (src/FFTBackend.cpp:211-232).  One thread
+// per m: Na coalesced sample loads, Na-point register FFT, Na coalesced 8-byte
+// stores into the scratch y[frame][r][m] that wf_fft2_kernel<MODE_SPLIT> reads back
+// (from L2: the host sizes a batch of frames to stay cache-resident).
+// ---------------------------------------------------------------------------
+struct SplitParams {
+	const void   *iq;        // int16 or float32 interleaved I/Q
+	const float  *window;    // N floats
+	const float2 *tw;        // N entries exp(-2*pi*i*j/N)
+	c64          *y;         // [n_frames][Na][Nb]
+	long long     frame0;    // first frame of this batch
+	long long     hop;
+	int           log2n;
+	float         iq_gain;
+};
+
+template <int LOG2NA, bool F32IN>
+__global__ void __launch_bounds__(256)
+wf_split_kernel(const SplitParams p)
+{
+	constexpr int NA = 1 << LOG2NA;
+	const int N = 1 << p.log2n;
+	const int NB = N >> LOG2NA;
+	const int m = blockIdx.x * 256 + threadIdx.x;              // < NB (NB is a multiple of 256)
+	const long long base = (p.frame0 + blockIdx.y) * p.hop;
+	const c64 gain2 = pk(0.f, p.iq_gain);
+
+	c64 v[NA];
+#pragma unroll
+	for (int q = 0; q < NA; q++) {
+		const int s = q * NB + m;
+		c64 x;
+		if (F32IN) x = __ldg(reinterpret_cast<const unsigned long long *>(p.iq) + base + s);
+		else x = short2_to_c64(__ldg(reinterpret_cast<const unsigned int *>(p.iq) + base + s));
+		const float w = __ldg(p.window + s);
+		v[q] = mul2(add2(x, gain2), pk(w, w));
+	}
+	fft_dif2<NA>(v);
+	c64 b[LOG2NA];
+	const unsigned long long *tw64 = reinterpret_cast<const unsigned long long *>(p.tw);
+#pragma unroll
+	for (int i = 0; i < LOG2NA; i++) b[i] = __ldg(tw64 + ((m << i) & (N - 1)));
+	twiddle_powers2<NA>(v, b);
+	c64 *dst = p.y + ((long long)blockIdx.y * NA) * NB + m;
+#pragma unroll
+	for (int r = 0; r < NA; r++) dst[(long long)r * NB] = v[bitrev(r, LOG2NA)];
 }
 
 }  // namespace ro

@@ -5,21 +5,33 @@
 
 namespace ro {
 
+enum { V2_DIRECT = 0, V2_STAGED = 1, V2_SPLIT = 2 };   // = MODE_* of ro_kernels2.cuh
+
 struct V2Kernel {
 	const void *fn;      // kernel symbol (for attribute / occupancy queries)
 	int         threads;
 	size_t      smem;
 	int         log2n;
-	bool        stage;
+	int         mode;
 	bool        gain;
 };
 
 // Picks the instantiation for N = 2^log2n; returns false when v2 has none.
-bool v2_pick(int log2n, bool stage, bool gain, V2Kernel *out);
+// mode V2_SPLIT exists for log2n = 14 only (the in-CTA part of longer frames).
+bool v2_pick(int log2n, int mode, bool gain, V2Kernel *out);
 
-// Launches it: n_frames frames of `hop`-spaced N-sample windows of d_iq (int16 I/Q).
+// Launches it: n_frames items of `hop`-spaced N-sample windows of d_iq (int16 I/Q), or, for
+// V2_SPLIT, n_frames = frames*Na items of N packed complex floats each (d_iq = the scratch
+// written by v2_launch_split), whose outputs interleave into rows of Na*N floats; `pair` != 0
+// promises 16-byte aligned rows and an even frames_per_cta (classes r, r+1 are stored together).
 cudaError_t v2_launch(const V2Kernel &k, int grid, cudaStream_t s, const void *d_iq, const float *d_window_half,
                       const float2 *d_tw, float *d_rows, long long row_stride, long long n_frames, long long hop,
-                      long long frames_per_cta, float iq_gain);
+                      long long frames_per_cta, float iq_gain, int log2na, int pair);
+
+// First radix-Na step of frames frame0 .. frame0+n_frames-1 (N = 2^log2n points, Na = 2^log2na)
+// into d_y[n_frames][Na][N/Na] (packed complex float).  f32in: float32 I/Q instead of int16.
+cudaError_t v2_launch_split(cudaStream_t s, int log2n, int log2na, bool f32in, const void *d_iq,
+                            const float *d_window, const float2 *d_tw, void *d_y, long long frame0,
+                            long long n_frames, long long hop, float iq_gain);
 
 }  // namespace ro

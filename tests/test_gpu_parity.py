@@ -53,7 +53,22 @@ def test_rows_match_oracle_large(bins, overlap):
     wf.close()
 
 
-@pytest.mark.parametrize("bins,overlap", [(4096, 2048), (16384, 12288), (32768, 24576)])
+def test_long_frames_cross_scratch_batches(monkeypatch):
+    """N > 16384 runs as split kernel + per-class transforms over a cache-sized scratch; with a
+    1 MiB budget the scratch holds one wave (74 frames of 32k), so 200 frames take three batches."""
+    monkeypatch.setenv("RO_SCRATCH_MB", "1")
+    bins, overlap = 32768, 24576
+    n = bins + 199 * (bins - overlap) + 17
+    iq = station_iq(n, 96000, seed=99)
+    wf = ro.Waterfall(bins, overlap, sample_rate=96000, in_format=ro.IN_INT16)
+    rows, _, nf = wf.process_host(iq)
+    ref = R.waterfall_rows(iq, bins, overlap)
+    assert nf == len(ref) == 200
+    assert_rows_close(rows, ref, "N=32768, 200 frames, 3 scratch batches")
+    wf.close()
+
+
+@pytest.mark.parametrize("bins,overlap", [(4096, 2048), (16384, 12288), (32768, 24576), (262144, 0)])
 def test_rows_match_oracle_float32_and_gain(bins, overlap):
     n = bins * 2 + 3 * (bins - overlap)
     spec = synth.SynthSpec(sample_rate=96000, n_samples=n, seed=7, carrier_freq=22000.3)
