@@ -37,6 +37,7 @@ struct Wf2Params {
 	long long     frames_per_cta;
 	float         iq_gain;
 	int           log2na;       // MODE_SPLIT: the frame has Na = 2^log2na residue classes of N points each
+	int           stagger;      // serialise the shared-memory load bursts of the warps that share a scheduler
 	int           pair;         // MODE_SPLIT: rows are 16-byte aligned and every CTA starts on an even item:
 	                            // classes r, r+1 are stored together (see the store stage)
 };
@@ -74,6 +75,20 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned int 
 		"bra WAIT_%=;\n\t"
 		"DONE_%=:\n\t}"
 		:: "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// Warps w, w+4, w+8, ... share one of the SM's four schedulers.  Left alone they issue their
+// shared-memory load bursts in lock step, receive their data together, then fight for the FMA
+// pipe together: load time and FMA time add up.  With the chain below the warp of level l starts
+// its burst only when the warp of level l-1 on the same scheduler has issued all of its own, so
+// the first warp computes while the next ones load.  Named barriers 1 + 3*q + l (q = scheduler,
+// l = level), 64 threads each: the producer arrives without blocking, the consumer syncs.
+__device__ __forceinline__ void chain_wait(int q, int l)
+{
+	if (l > 0) asm volatile("bar.sync %0, 64;" :: "r"(3 * q + l) : "memory");
+}
+__device__ __forceinline__ void chain_pass(int q, int l, int levels)
+{
+	if (l + 1 < levels) asm volatile("bar.arrive %0, 64;" :: "r"(3 * q + l + 1) : "memory");
 }
 // global -> shared bulk copy (TMA), bytes a multiple of 16, both addresses 16-byte aligned
 __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned int bytes, unsigned long long *bar)
@@ -122,6 +137,9 @@ wf_fft2_kernel(const Wf2Params p)
 	unsigned int *ring = reinterpret_cast<unsigned int *>(mbar + 4);
 
 	const int t = threadIdx.x;
+	constexpr int LEVELS = T / 128;            // warps per scheduler
+	constexpr bool CHAIN = LEVELS >= 2 && LEVELS <= 4;
+	const int wq = (t >> 5) & 3, wl = t >> 7;
 	const long long f0 = (long long)blockIdx.x * p.frames_per_cta;
 	long long f1 = f0 + p.frames_per_cta;
 	if (f1 > p.n_frames) f1 = p.n_frames;
@@ -167,12 +185,19 @@ wf_fft2_kernel(const Wf2Params p)
 			const int base = (int)(((f - f0) * hop) & NMASK);
 			mbar_wait(mbar, parity);
 			parity ^= 1u;
+			if (CHAIN && (p.stagger & 1)) chain_wait(wq, wl);
+			unsigned int raw[R1];
+			float wv[R1];
 #pragma unroll
 			for (int n1 = 0; n1 < R1; n1++) {
-				const int s = n1 * M + t;
-				const c64 x = short2_to_c64(ring[(base + s) & NMASK]);
-				const float w = (n1 < R1 / 2) ? win[n1 * M + t] : win[(R1 - 1 - n1) * M + (M - 1 - t)];
-				v[n1] = mul2(GAIN ? add2(x, gain2) : x, pk(w, w));
+				raw[n1] = ring[(base + n1 * M + t) & NMASK];
+				wv[n1] = (n1 < R1 / 2) ? win[n1 * M + t] : win[(R1 - 1 - n1) * M + (M - 1 - t)];
+			}
+			if (CHAIN && (p.stagger & 1)) chain_pass(wq, wl, LEVELS);
+#pragma unroll
+			for (int n1 = 0; n1 < R1; n1++) {
+				const c64 x = short2_to_c64(raw[n1]);
+				v[n1] = mul2(GAIN ? add2(x, gain2) : x, pk(wv[n1], wv[n1]));
 			}
 		} else if (SPLIT) {
 			const unsigned long long *src = reinterpret_cast<const unsigned long long *>(p.iq) + f * N;
@@ -221,8 +246,10 @@ wf_fft2_kernel(const Wf2Params p)
 		// ---- pass 2 ----
 		{
 			const int k1 = t / R3, n3 = t % R3;
+			if (CHAIN && (p.stagger & 2)) chain_wait(wq, wl);
 #pragma unroll
 			for (int n2 = 0; n2 < R2; n2++) v[n2] = S[k1 * ROW1 + n2 * R3 + n3];
+			if (CHAIN && (p.stagger & 2)) chain_pass(wq, wl, LEVELS);
 			mbar_arrive(bar_rd2);                       // my pass-2 inputs are in registers
 			fft_dif2<R2>(v);
 			twiddle_powers2<R2>(v, b2);
@@ -242,6 +269,7 @@ wf_fft2_kernel(const Wf2Params p)
 			const int pbase = G * t;
 			const int k1b = pbase % R1, k2 = pbase / R1;
 			c64 (&u)[P] = v;                       // u[c*R3 + n3]
+			if (CHAIN && (p.stagger & 4)) chain_wait(wq, wl);
 #pragma unroll
 			for (int n3 = 0; n3 < R3; n3++) {
 				constexpr int GM = G - 1;
@@ -254,6 +282,7 @@ wf_fft2_kernel(const Wf2Params p)
 					u[((2 * h2 + 1) ^ (sw & GM)) * R3 + n3] = q.y;
 				}
 			}
+			if (CHAIN && (p.stagger & 4)) chain_pass(wq, wl, LEVELS);
 			mbar_arrive(bar_rd3);                      // my pass-3 inputs are in registers
 			float mag[R3][G];
 #pragma unroll

@@ -67,7 +67,7 @@ bool v2_pick(int log2n, int mode, bool gain, V2Kernel *out)
 
 cudaError_t v2_launch(const V2Kernel &k, int grid, cudaStream_t s, const void *d_iq, const float *d_window_half,
                       const float2 *d_tw, float *d_rows, long long row_stride, long long n_frames, long long hop,
-                      long long frames_per_cta, float iq_gain, int log2na, int pair)
+                      long long frames_per_cta, float iq_gain, int log2na, int pair, int stagger)
 {
 	Wf2Params p;
 	p.iq = d_iq;
@@ -81,6 +81,7 @@ cudaError_t v2_launch(const V2Kernel &k, int grid, cudaStream_t s, const void *d
 	p.iq_gain = iq_gain;
 	p.log2na = log2na;
 	p.pair = pair;
+	p.stagger = stagger;
 	void *args[] = { &p };
 	return cudaLaunchKernel(k.fn, dim3(grid), dim3(k.threads), args, k.smem, s);
 }

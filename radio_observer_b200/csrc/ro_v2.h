@@ -26,7 +26,7 @@ bool v2_pick(int log2n, int mode, bool gain, V2Kernel *out);
 // promises 16-byte aligned rows and an even frames_per_cta (classes r, r+1 are stored together).
 cudaError_t v2_launch(const V2Kernel &k, int grid, cudaStream_t s, const void *d_iq, const float *d_window_half,
                       const float2 *d_tw, float *d_rows, long long row_stride, long long n_frames, long long hop,
-                      long long frames_per_cta, float iq_gain, int log2na, int pair);
+                      long long frames_per_cta, float iq_gain, int log2na, int pair, int stagger);
 
 // First radix-Na step of frames frame0 .. frame0+n_frames-1 (N = 2^log2n points, Na = 2^log2na)
 // into d_y[n_frames][Na][N/Na] (packed complex float).  f32in: float32 I/Q instead of int16.
