@@ -540,7 +540,8 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 	h->split_ok = false;
 	// passes 2 and 3 chained (bits 1, 2): +19 % on the 16k kernel (B200, 21.0 -> 25.0 M frames/s);
 	// chaining pass 1 as well (bit 0) costs 5 %: its warps already arrive staggered from pass 3
-	h->stagger = 6;
+	// bit 3: the pass-2 chain releases the warp two levels down (0.7 .. 3.9 % over distance 1)
+	h->stagger = 14;
 	if (const char *e4 = getenv("RO_STAGGER")) h->stagger = atoi(e4);
 	int log2nb = 14;                              // in-CTA transform of the split path
 	if (const char *e3 = getenv("RO_SPLIT_LOG2NB")) log2nb = atoi(e3);

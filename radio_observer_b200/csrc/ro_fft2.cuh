@@ -73,6 +73,67 @@ __device__ __forceinline__ void fft_dif2(c64 (&v)[R])
 	}
 }
 
+__device__ __forceinline__ c64 neg2(c64 v) { float a, b; upk(v, a, b); return pk(-a, -b); }
+
+// Same transform, same register convention (input n at v[n], output k at
+// v[bitrev(k)]), decimation in TIME: the in-place array a[i] is the view
+// v[bitrev(i)], so the bit-reversed input order DIT wants costs nothing.
+// Why: a DIT butterfly applies its twiddle BEFORE the add/sub, so the product
+// folds into the sum,
+//     A' = A + w*B  = fma(swap(B), (s,-s), fma(B, (c,c), A))      w = c - i*s
+//     B' = A - w*B  = fma(A, 2, -A')
+// three FFMA2 where DIF needs four instructions (add, sub, mul, fma), and a
+// multiplication by -i is a lane swap with signs inside the two fmas.  32 points:
+// 194 packed instructions instead of 228; 16 points: 74 instead of 84.
+template <int R>
+__device__ __forceinline__ void fft_dit2(c64 (&v)[R])
+{
+	static_assert(R >= 2 && R <= 32 && (R & (R - 1)) == 0, "radix");
+	constexpr int L = ilog2(R);
+	// in v-space level lvl pairs v[i], v[i + (R >> (lvl+1))] like DIF does, but the twiddle is
+	// constant over a block: W_{2^(lvl+1)}^j with j = bitrev(block number, lvl)
+	constexpr int BR5[32] = {0, 16, 8, 24, 4, 20, 12, 28, 2, 18, 10, 26, 6, 22, 14, 30,
+	                         1, 17, 9, 25, 5, 21, 13, 29, 3, 19, 11, 27, 7, 23, 15, 31};
+#pragma unroll
+	for (int lvl = 0; lvl < L; lvl++) {
+		const int vhalf = R >> (lvl + 1);
+#pragma unroll
+		for (int blk = 0; blk < (1 << lvl); blk++) {
+			const int e = (BR5[blk] >> (5 - lvl)) * (16 >> lvl);   // W_32^e
+#pragma unroll
+			for (int off = 0; off < vhalf; off++) {
+				const int ia = blk * 2 * vhalf + off, ib = ia + vhalf;
+				const c64 a = v[ia], b = v[ib];
+				if (e == 0) {
+					v[ia] = add2(a, b);
+					v[ib] = sub2(a, b);
+				} else if (e == 8) {                      // w = -i:  w*b = (b.im, -b.re)
+					v[ia] = fma2(swp(b), pk(1.f, -1.f), a);
+					v[ib] = fma2(swp(b), pk(-1.f, 1.f), a);
+				} else {
+					const float c = cw32(e), sn = sw32(e);
+					const c64 a2 = fma2(swp(b), pk(sn, -sn), fma2(b, pk(c, c), a));
+					v[ia] = a2;
+					v[ib] = fma2(a, pk(2.f, 2.f), neg2(a2));
+				}
+			}
+		}
+	}
+}
+
+// The transform the kernels call.  Measured on B200 (gpurun_out/r01k_sweep_*.jsonl): DIT is 2-5 %
+// faster in the one-kernel path (1k..16k), DIF 2.5 % faster in the long-frame path, whose 16k stage
+// waits on global loads, not on the FMA pipe.  RO_DIT=0 forces DIF everywhere (A/B measurements).
+#ifndef RO_DIT
+#define RO_DIT 1
+#endif
+template <int R, bool DIT>
+__device__ __forceinline__ void fft_fwd2(c64 (&v)[R])
+{
+	if (RO_DIT && DIT) fft_dit2<R>(v);
+	else fft_dif2<R>(v);
+}
+
 // Multiply output k (at v[bitrev(k)]) by w^k, k = 1..R-1; base[i] = w^(2^i)
 // read from the once-rounded table.  Same composition as twiddle_powers().
 template <int R>

@@ -102,6 +102,17 @@ __device__ __forceinline__ void ptxas_fence(int never)
 {
 	if (never) asm volatile("bar.sync 15, 32;" ::: "memory");
 }
+// Further fence sites, selected at compile time (-DRO_FENCE_SITES=mask for the 8k and 16k kernels,
+// -DRO_FENCE_SITES_SMALL=mask for the others).  Bit 4 = after each R3-point transform of pass 3:
+// measured +3 % on the 16k kernel (25.2 -> 26.1 M frames/s) and +2.5 % on the 8k one, -4 % at 1k;
+// every other site within noise.
+#ifndef RO_FENCE_SITES
+#define RO_FENCE_SITES 16
+#endif
+#ifndef RO_FENCE_SITES_SMALL
+#define RO_FENCE_SITES_SMALL 0
+#endif
+#define RO_SITE(bit, never) do { if ((LOG2N >= 13 ? RO_FENCE_SITES : RO_FENCE_SITES_SMALL) & (1 << (bit))) ptxas_fence(never); } while (0)
 // global -> shared bulk copy (TMA), bytes a multiple of 16, both addresses 16-byte aligned
 __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned int bytes, unsigned long long *bar)
 {
@@ -139,6 +150,14 @@ wf_fft2_kernel(const Wf2Params p)
 	constexpr int SW = 16 / R3;
 	constexpr int NMASK = N - 1;
 	constexpr unsigned int CHUNK = 16384;      // bytes per bulk copy
+	// Pass 2 writes its outputs back into the row of S it read (see pass 2): 32*32*16 only.
+	// Correct (parity tests pass) but measured SLOWER on B200, 25.7 against 27.1 M frames/s: without
+	// the wait the early warps' store bursts collide with the load bursts of the chained late warps.
+	// Off; kept for A/B measurements (-DRO_INPLACE=1).
+#ifndef RO_INPLACE
+#define RO_INPLACE 0
+#endif
+	constexpr bool INPLACE = RO_INPLACE && R3 == 16 && P == 32;
 
 	extern __shared__ __align__(128) unsigned char smem_raw[];
 	c64 *S = reinterpret_cast<c64 *>(smem_raw);
@@ -238,8 +257,10 @@ wf_fft2_kernel(const Wf2Params p)
 		}
 
 		// ---- pass 1 ----
-		fft_dif2<R1>(v);
+		fft_fwd2<R1, !SPLIT>(v);
+		RO_SITE(0, p.stagger & 1);
 		twiddle_powers2<R1>(v, b1);
+		RO_SITE(1, p.stagger & 1);
 		// S still holds the previous frame's pass-3 inputs until every thread has read them
 		if (f > f0) mbar_wait(bar_rd3, (unsigned int)(f - 1 - f0) & 1u);
 #pragma unroll
@@ -267,19 +288,35 @@ wf_fft2_kernel(const Wf2Params p)
 		}
 
 		// ---- pass 2 ----
+		// Row k1 of S (R2*R3 points) is read and transformed by the R3 threads (k1, n3) alone, all in one
+		// warp.  INPLACE: they write output (k2, n3) back into slot k2*R3 + n3 of the SAME row, so no
+		// thread has to wait for the loads of any other warp (the split barrier bar_rd2 was the second
+		// largest stall: every warp held its stores until the last chained warp had loaded); loads and
+		// stores of one warp reach shared memory in program order.  The 16-byte units of a slot group are
+		// XOR-permuted by k1/2 so that pass 3, whose quarter-warps read the same unit of 8 different rows,
+		// finds them in 8 different bank groups.
 		{
 			const int k1 = t / R3, n3 = t % R3;
 			if (CHAIN && (p.stagger & 2)) chain_wait(wq, wl, cdist);
 #pragma unroll
 			for (int n2 = 0; n2 < R2; n2++) v[n2] = S[k1 * ROW1 + n2 * R3 + n3];
 			if (CHAIN && (p.stagger & 2)) chain_pass(wq, wl, LEVELS, cdist);
-			mbar_arrive(bar_rd2);                       // my pass-2 inputs are in registers
-			fft_dif2<R2>(v);
+			if (!INPLACE) mbar_arrive(bar_rd2);         // my pass-2 inputs are in registers
+			fft_fwd2<R2, !SPLIT>(v);
+			RO_SITE(2, p.stagger & 1);
 			twiddle_powers2<R2>(v, b2);
-			mbar_wait(bar_rd2, (unsigned int)(f - f0) & 1u);   // ... and so are everyone else's
-			const int col = k1 ^ (n3 * SW);
+			RO_SITE(3, p.stagger & 1);
+			if (INPLACE) {
+				__syncwarp();
+				c64 *dst = S + k1 * ROW1 + (n3 ^ (((k1 >> 1) & 7) << 1));
 #pragma unroll
-			for (int k2 = 0; k2 < R2; k2++) S[(k2 * R3 + n3) * R1 + col] = v[bitrev(k2, LP)];
+				for (int k2 = 0; k2 < R2; k2++) dst[k2 * R3] = v[bitrev(k2, LP)];
+			} else {
+				mbar_wait(bar_rd2, (unsigned int)(f - f0) & 1u);   // ... and so are everyone else's
+				const int col = k1 ^ (n3 * SW);
+#pragma unroll
+				for (int k2 = 0; k2 < R2; k2++) S[(k2 * R3 + n3) * R1 + col] = v[bitrev(k2, LP)];
+			}
 		}
 		__syncthreads();
 
@@ -293,6 +330,20 @@ wf_fft2_kernel(const Wf2Params p)
 			const int k1b = pbase % R1, k2 = pbase / R1;
 			c64 (&u)[P] = v;                       // u[c*R3 + n3]
 			if (CHAIN && (p.stagger & 4)) chain_wait(wq, wl, cdist3);
+			if (INPLACE) {
+				// row k1b + c, slots k2*R3 .. k2*R3 + R3-1: R3/2 128-bit loads, unit L sits at L ^ (k1/2 & 7)
+#pragma unroll
+				for (int c = 0; c < G; c++) {
+					const int k1 = k1b + c;
+					const unsigned int a0 = (unsigned int)((k1 * ROW1 + k2 * R3) * 8) ^ (unsigned int)(((k1 >> 1) & 7) << 4);
+#pragma unroll
+					for (int L = 0; L < R3 / 2; L++) {
+						const ulonglong2 q = *reinterpret_cast<const ulonglong2 *>(reinterpret_cast<const unsigned char *>(S) + (a0 ^ (unsigned int)(L << 4)));
+						u[c * R3 + 2 * L] = q.x;
+						u[c * R3 + 2 * L + 1] = q.y;
+					}
+				}
+			} else {
 #pragma unroll
 			for (int n3 = 0; n3 < R3; n3++) {
 				constexpr int GM = G - 1;
@@ -305,6 +356,7 @@ wf_fft2_kernel(const Wf2Params p)
 					u[((2 * h2 + 1) ^ (sw & GM)) * R3 + n3] = q.y;
 				}
 			}
+			}
 			if (CHAIN && (p.stagger & 4)) chain_pass(wq, wl, LEVELS, cdist3);
 			mbar_arrive(bar_rd3);                      // my pass-3 inputs are in registers
 			float mag[R3][G];
@@ -313,14 +365,16 @@ wf_fft2_kernel(const Wf2Params p)
 				c64 w[R3];
 #pragma unroll
 				for (int n3 = 0; n3 < R3; n3++) w[n3] = u[c * R3 + n3];
-				fft_dif2<R3>(w);
+				fft_fwd2<R3, !SPLIT>(w);
 #pragma unroll
 				for (int k3 = 0; k3 < R3; k3++) {
 					float zr, zi;
 					upk(w[bitrev(k3, L3)], zr, zi);
 					mag[k3][c] = fast_sqrt(fmaf(zr, zr, zi * zi));
 				}
+				RO_SITE(4, p.stagger & 1);
 			}
+			RO_SITE(5, p.stagger & 1);
 			if (SPLIT) {
 				// output k of residue class r is bin Na*k + r of the Na*N-point frame
 				const int la = p.log2na;
@@ -385,7 +439,7 @@ wf_fft2_kernel(const Wf2Params p)
 #pragma unroll
 			for (int n3 = 0; n3 < R3; n3++) u[n3] = S[((t / R1) * R3 + n3) * R1 + ((t % R1) ^ (n3 * SW))];
 			mbar_arrive(bar_rd3);
-			fft_dif2<R3>(u);
+			fft_fwd2<R3, !SPLIT>(u);
 #pragma unroll
 			for (int k3 = 0; k3 < R3; k3++) {
 				const int off = (k3 * (N / R3) + N / 2) & NMASK;   // t < N/R3 = T
@@ -440,7 +494,7 @@ wf_split_kernel(const SplitParams p)
 		const float w = __ldg(p.window + s);
 		v[q] = mul2(add2(x, gain2), pk(w, w));
 	}
-	fft_dif2<NA>(v);
+	fft_fwd2<NA, false>(v);
 	c64 b[LOG2NA];
 	const unsigned long long *tw64 = reinterpret_cast<const unsigned long long *>(p.tw);
 #pragma unroll

@@ -36,6 +36,7 @@ bool v2_pick(int log2n, int mode, bool gain, V2Kernel *out)
 		out->mode = mode;
 		out->gain = false;                       // the gain is applied by the split kernel
 		switch (log2n) {
+#ifndef RO_EXP_ONLY14
 		case 12:
 			out->threads = (1 << 12) / 16;
 			out->smem = wf2_smem_bytes<12, 16, 16, MODE_SPLIT>();
@@ -46,6 +47,7 @@ bool v2_pick(int log2n, int mode, bool gain, V2Kernel *out)
 			out->smem = wf2_smem_bytes<13, 32, 8, MODE_SPLIT>();
 			out->fn = (const void *)wf_fft2_kernel<13, 32, 8, MODE_SPLIT, false, 2>;
 			return true;
+#endif
 		case 14:
 			out->threads = (1 << 14) / 32;
 			out->smem = wf2_smem_bytes<14, 32, 16, MODE_SPLIT>();
@@ -56,10 +58,12 @@ bool v2_pick(int log2n, int mode, bool gain, V2Kernel *out)
 		}
 	}
 	switch (log2n) {
+#ifndef RO_EXP_ONLY14
 	case 10: return pick_one<10, 16, 4, 12, 12>(mode, gain, out);
 	case 11: return pick_one<11, 16, 8, 6, 6>(mode, gain, out);
 	case 12: return pick_one<12, 16, 16, 3, 3>(mode, gain, out);
 	case 13: return pick_one<13, 32, 8, 2, 2>(mode, gain, out);
+#endif
 	case 14: return pick_one<14, 32, 16, 1, 1>(mode, gain, out);
 	default: return false;
 	}
