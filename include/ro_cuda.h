@@ -61,7 +61,14 @@ typedef struct ro_wf_config {
 	int32_t avg_bins;                /* bins averaged around the peak             */
 	int32_t device;                  /* CUDA device ordinal                        */
 	int32_t max_batch_frames;        /* 0 = default; frames per kernel launch in the streaming path */
-	int32_t reserved[6];
+	/* Extension stages, no reference counterpart: 0 or 1 = off, which keeps the
+	 * reference's rows.  When on, an output row is the RMS amplitude of row_avg consecutive
+	 * waterfall rows x bin_decim adjacent bins, sqrt(mean |X|^2); a group of rows left incomplete at
+	 * ro_wf_flush / at the end of a batch call is dropped like the reference drops an incomplete
+	 * frame.  Bands and detector bins then index the REDUCED row (bins / bin_decim wide). */
+	int32_t row_avg;                 /* rows accumulated per output row, >= 1                      */
+	int32_t bin_decim;               /* adjacent bins per output bin: power of two, 1 .. 128       */
+	int32_t reserved[4];
 } ro_wf_config;
 
 /* Per-row detector statistics: what BolidRecorder::update computes before its
@@ -86,6 +93,8 @@ void ro_wf_destroy(ro_wf *h);
 int  ro_wf_row_width(const ro_wf *h);
 /* the clamped overlap actually in use */
 int  ro_wf_overlap(const ro_wf *h);
+/* floats per row on the DEVICE: bins / bin_decim */
+int  ro_wf_out_bins(const ro_wf *h);
 
 /* ---- streaming path (Backend::process, src/FFTBackend.cpp:192-279) ------ */
 
@@ -114,11 +123,14 @@ int  ro_wf_reset(ro_wf *h);
 
 /* Number of frames n_samples yield: floor((S-N)/hop)+1, or 0. */
 size_t ro_wf_frame_count(const ro_wf *h, size_t n_samples);
+/* Number of OUTPUT rows n_samples yield: frame_count / row_avg. */
+size_t ro_wf_row_count(const ro_wf *h, size_t n_samples);
 
 /* Input already in device memory (d_iq: cfg.in_format, int16 or float32).
- * Writes FULL rows (bins floats each, fftshifted) to d_rows and, if the
- * detector is configured and d_det != NULL, one record per row.  Asynchronous
- * on the handle's stream unless `sync` is non-zero. */
+ * Writes FULL rows (ro_wf_out_bins floats each, fftshifted) to d_rows and, if the
+ * detector is configured and d_det != NULL, one record per row; max_frames and
+ * *n_frames count output rows.  Asynchronous on the handle's stream unless
+ * `sync` is non-zero. */
 int  ro_wf_process_resident(ro_wf *h, const void *d_iq, size_t n_samples,
                             float *d_rows, ro_det_rec *d_det,
                             size_t max_frames, size_t *n_frames, int sync);
@@ -131,6 +143,11 @@ int  ro_wf_process_host(ro_wf *h, const void *iq, size_t n_samples,
                         size_t max_frames, size_t *n_frames);
 
 /* ---- stage variants (unit tests, ncu attribution) ------------------------ */
+
+/* Only the reduction kernel (row_avg x bin_decim of the handle): n_in full rows of `bins` floats
+ * -> n_in / row_avg rows of bins / bin_decim floats. */
+int  ro_wf_reduce_resident(ro_wf *h, const float *d_rows, size_t n_in, float *d_out,
+                           size_t *n_out, int sync);
 
 /* Only the detector kernel over n_rows full rows already on the device. */
 int  ro_wf_detect_resident(ro_wf *h, const float *d_rows, size_t n_rows,

@@ -321,6 +321,23 @@ def detector_rows(rows: np.ndarray, d: DetectorBands):
 
 
 # --------------------------------------------------------------------------
+# Extension stages row_avg / bin_decim (NO reference counterpart: SURVEY.md D2;
+# the reference's row rate is set by `overlap` alone, src/FFTBackend.cpp:150-151,
+# 241-245, and its only bin reduction is the band crop, src/WaterfallBackend.cpp:
+# 368-380).  Definition restated here so the CUDA stage has a checker:
+#   out[j][i] = sqrt(mean over r < R, d < D of rows[j*R + r][i*D + d]^2)
+# computed in float64, rounded once to float32; an incomplete last group is dropped.
+# --------------------------------------------------------------------------
+def reduce_rows(rows: np.ndarray, row_avg: int = 1, bin_decim: int = 1) -> np.ndarray:
+    R_, D_ = max(1, int(row_avg)), max(1, int(bin_decim))
+    F, N = rows.shape
+    G = F // R_
+    x = rows[:G * R_].astype(np.float64)
+    p = (x * x).reshape(G, R_, N // D_, D_).sum(axis=(1, 3)) / float(R_ * D_)
+    return np.sqrt(p).astype(np.float32)
+
+
+# --------------------------------------------------------------------------
 # Row ring index arithmetic                           src/RingBuffer.h:428-571
 # --------------------------------------------------------------------------
 def ring_capacity(bins: int, chunk_bytes: int, min_rows: int) -> int:

@@ -10,7 +10,10 @@ from .capi import (  # noqa: F401
     window_table, twiddle_table, IN_INT16, IN_FLOAT32, IN_COMPLEX64,
 )
 
+from . import archive  # noqa: F401,E402  (time-sharded archive reprocessing, host-side trigger state machine)
+
 __all__ = [
+    "archive",
     "RoError", "WfConfig", "DetRec", "Waterfall", "load_library", "library_path",
     "window_table", "twiddle_table", "IN_INT16", "IN_FLOAT32", "IN_COMPLEX64",
 ]

@@ -1,0 +1,228 @@
+"""archive.py -- time-sharded archive reprocessing (BASELINE config 4).
+
+The waterfall path shards by TIME with no exchange between GPUs: frames are independent
+(reference src/FFTBackend.cpp:192-279 forms frame k from samples [k*hop, k*hop + bins) and nothing
+else), so rank g of G takes frames [floor(g*F/G), floor((g+1)*F/G)) and reads its samples -- plus a
+halo of `overlap` samples that the next shard also reads -- straight from the input.  Rows and
+detector records are concatenated in frame order on the host.  No data-path collective, no NCCL;
+`torch.distributed` (any backend, gloo on the host) is used only to hand the per-rank results to
+rank 0.
+
+The order-dependent remainder is O(1) per row and runs once over the merged records:
+`BolidTrigger` is the decision and state machine of BolidRecorder::update
+(reference src/BolidRecorder.cpp:119-299) in GLOBAL row numbers.
+
+Host-side Hz<->bin arithmetic follows reference src/FFTBackend.h:134-200 with its float/double
+mixture (the band edges decide which bins the detector sees, so they must be bit-exact).
+
+Nothing here imports oracle/: the compute callable defaults to the CUDA library.
+"""
+from dataclasses import dataclass, field
+from typing import Callable, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+f32 = np.float32
+
+
+# ---------------------------------------------------------------------------
+# A9  Hz <-> bin (reference src/FFTBackend.h:134-200, src/FFTBackend.cpp:150-151)
+# ---------------------------------------------------------------------------
+def frequency_to_bin(freq: float, sample_rate: int, bins: int) -> int:
+    """clamp((int)(N_f * ((double)(f / sr_f) + 0.5)), 0, N-1); f/sr is a FLOAT division."""
+    q = f32(f32(freq) / f32(sample_rate))
+    v = float(f32(bins)) * (float(q) + 0.5)
+    return min(max(int(v), 0), bins - 1)
+
+
+def bin_to_frequency(b: int, sample_rate: int, bins: int) -> np.float32:
+    """(float)(sr_f * (-0.5 + (double)(b_f / N_f)))."""
+    return f32(float(f32(sample_rate)) * (-0.5 + float(f32(f32(b) / f32(bins)))))
+
+
+def fft_sample_rate(sample_rate: int, bins: int, overlap: int) -> np.float32:
+    """rows per second: (float)sr / (float)(bins - overlap)."""
+    return f32(f32(sample_rate) / f32(bins - overlap))
+
+
+def time_to_fft_samples(t: float, fsr: np.float32) -> int:
+    """reference src/FFTBackend.h:197-200: `return time * fftSampleRate_` (double * float -> int)."""
+    return int(float(t) * float(fsr))
+
+
+def clamp_overlap(bins: int, overlap: int) -> int:
+    """reference src/FFTBackend.cpp:108-109."""
+    return min(max(int(overlap), 0), bins - 1)
+
+
+def frame_count(n_samples: int, bins: int, overlap: int) -> int:
+    hop = bins - clamp_overlap(bins, overlap)
+    return 0 if n_samples < bins else (n_samples - bins) // hop + 1
+
+
+def bolid_bands(sample_rate: int, bins: int, overlap: int, *, low_detect_freq: float, hi_detect_freq: float,
+                low_noise_freq: float, hi_noise_freq: float, avg_freq_range: float,
+                advance_time: float = 1.0, jitter_time: float = 1.0) -> dict:
+    """The bin values BolidRecorder::start derives from its JSON keys
+    (reference src/BolidRecorder.cpp:80-103): detector config for `Waterfall(detector=...)`
+    plus the advance / jitter row counts of the state machine."""
+    dlo, dhi = sorted((frequency_to_bin(low_detect_freq, sample_rate, bins),
+                       frequency_to_bin(hi_detect_freq, sample_rate, bins)))
+    nlo, nhi = sorted((frequency_to_bin(low_noise_freq, sample_rate, bins),
+                       frequency_to_bin(hi_noise_freq, sample_rate, bins)))
+    avg = frequency_to_bin(avg_freq_range, sample_rate, bins) - frequency_to_bin(0.0, sample_rate, bins)
+    fsr = fft_sample_rate(sample_rate, bins, clamp_overlap(bins, overlap))
+    return dict(det_lo=dlo, det_w=dhi - dlo, noise_lo=nlo, noise_w=nhi - nlo, avg_bins=avg,
+                advance=time_to_fft_samples(advance_time, fsr), jitter=time_to_fft_samples(jitter_time, fsr))
+
+
+# ---------------------------------------------------------------------------
+# 8e  shard plan
+# ---------------------------------------------------------------------------
+@dataclass(frozen=True)
+class Shard:
+    rank: int
+    frame0: int        # first global frame (row) of the shard
+    frame1: int        # one past the last
+    sample0: int       # first input sample the shard reads
+    sample1: int       # one past the last (includes the overlap halo)
+
+    @property
+    def n_frames(self) -> int:
+        return self.frame1 - self.frame0
+
+    @property
+    def n_samples(self) -> int:
+        return self.sample1 - self.sample0
+
+
+def plan_shards(n_samples: int, bins: int, overlap: int, world: int) -> List[Shard]:
+    """Contiguous frame ranges, one per rank; an empty shard has sample0 == sample1."""
+    if world < 1:
+        raise ValueError("world must be >= 1")
+    ov = clamp_overlap(bins, overlap)
+    hop = bins - ov
+    F = frame_count(n_samples, bins, ov)
+    out = []
+    for g in range(world):
+        f0, f1 = (g * F) // world, ((g + 1) * F) // world
+        if f1 > f0:
+            out.append(Shard(g, f0, f1, f0 * hop, (f1 - 1) * hop + bins))
+        else:
+            out.append(Shard(g, f0, f0, f0 * hop, f0 * hop))
+    return out
+
+
+# ---------------------------------------------------------------------------
+# A14  detector decision + state machine over merged records
+# ---------------------------------------------------------------------------
+@dataclass
+class BolidEvent:
+    emit_row: int       # global row at which the event was emitted (jitter expired)
+    start_row: int      # first row of the snapshot: (row of first detection + 1) - advance; may be < 0
+    length: int         # rows: 2*advance + rows between first detection and the last gap
+    peak_bin: int       # row index of the peak of the FIRST detecting row (det_lo + peak)
+    noise: np.float32   # of the first detecting row
+    magnitude: np.float32
+    duration_s: np.float32
+
+
+@dataclass
+class BolidTrigger:
+    """BolidRecorder::update (reference src/BolidRecorder.cpp:119-299) on (noise, peak, avg)
+    records; `row` numbers are global, the ring index the reference uses is row mod capacity.
+    The threshold is the reference's hard-coded 2.0 (`threshold` JSON key is inert, :135)."""
+    det_lo: int
+    advance: int
+    jitter: int
+    fft_sample_rate: np.float32
+    events: List[BolidEvent] = field(default_factory=list)
+    _state: int = 0     # 0 INIT, 1 BOLID, 2 ENDED
+    _duration: int = 0
+    _row: int = 0
+    _start: int = 0
+    _length: int = 0
+    _first: Optional[Tuple[int, np.float32, np.float32]] = None
+
+    def feed(self, det: np.ndarray) -> None:
+        """det: structured records (noise, peak, avg) of consecutive rows, in row order."""
+        noise = np.asarray(det["noise"], dtype=np.float32)
+        avg = np.asarray(det["avg"], dtype=np.float32)
+        peak = np.asarray(det["peak"])
+        hit = avg.astype(np.float64) > noise.astype(np.float64) * 2.0
+        for i in range(len(hit)):
+            r = self._row
+            self._row += 1
+            if self._state == 0:
+                if hit[i]:
+                    self._first = (self.det_lo + int(peak[i]), noise[i], avg[i])
+                    self._duration = 1
+                    self._start = (r + 1) - self.advance       # mark() is the index of the NEXT row
+                    self._length = 2 * self.advance
+                    self._state = 1
+            elif self._state == 1:
+                if hit[i]:
+                    self._duration += 1
+                else:
+                    self._length += self._duration
+                    self._duration = 1
+                    self._state = 2
+            else:
+                self._duration += 1
+                if hit[i]:
+                    self._state = 1
+                elif self._duration >= self.jitter:
+                    pb, n0, a0 = self._first
+                    dur = f32(f32(self._length - 2 * self.advance) / f32(self.fft_sample_rate))
+                    self.events.append(BolidEvent(r, self._start, self._length, pb, n0, a0, dur))
+                    self._state = 0
+
+
+# ---------------------------------------------------------------------------
+# driver: one rank's shard, then the merge on rank 0
+# ---------------------------------------------------------------------------
+def default_compute(bins: int, overlap: int, sample_rate: int, bands: Sequence[Tuple[int, int]],
+                    detector: Optional[dict], device: int) -> Callable:
+    """The product compute: ro_wf_process_host on `device` (fails loudly without the CUDA library)."""
+    from .capi import Waterfall, IN_INT16
+    det = None if detector is None else {k: detector[k] for k in ("det_lo", "det_w", "noise_lo", "noise_w", "avg_bins")}
+    wf = Waterfall(bins, overlap, sample_rate=sample_rate, in_format=IN_INT16, bands=list(bands), detector=det,
+                   device=device)
+
+    def run(iq_int16: np.ndarray):
+        rows, recs, n = wf.process_host(iq_int16)
+        return rows[:n], (None if recs is None else recs[:n])
+    return run
+
+
+def reprocess_archive(iq: np.ndarray, bins: int, overlap: int, *, sample_rate: int = 96000,
+                      bands: Sequence[Tuple[int, int]] = (), detector: Optional[dict] = None,
+                      rank: int = 0, world: int = 1, dist=None, device: Optional[int] = None,
+                      compute: Optional[Callable] = None):
+    """Process this rank's time shard of `iq` (interleaved int16 [I,Q], e.g. a numpy memmap of the
+    archive: only the shard's slice is read) and merge on rank 0.
+
+    Returns (rows, det, shards) on rank 0 -- rows of all shards concatenated in frame order -- and
+    (None, None, shards) elsewhere.  `dist` is an initialised torch.distributed module when
+    world > 1; it carries only the finished rows to rank 0 (host tensors)."""
+    n_samples = iq.shape[0] // 2
+    shards = plan_shards(n_samples, bins, overlap, world)
+    me = shards[rank]
+    if compute is None:
+        compute = default_compute(bins, overlap, sample_rate, bands, detector, rank if device is None else device)
+    if me.n_frames > 0:
+        rows, det = compute(np.ascontiguousarray(iq[2 * me.sample0:2 * me.sample1]))
+        if rows.shape[0] != me.n_frames:
+            raise RuntimeError(f"rank {rank}: shard of {me.n_frames} frames produced {rows.shape[0]} rows")
+    else:
+        rows, det = None, None
+    if world == 1:
+        return rows, det, shards
+    parts = [None] * world if rank == 0 else None
+    dist.gather_object((rows, det), parts, dst=0)
+    if rank != 0:
+        return None, None, shards
+    have = [p for p in parts if p[0] is not None]
+    all_rows = np.concatenate([p[0] for p in have]) if have else None
+    all_det = np.concatenate([p[1] for p in have]) if have and have[0][1] is not None else None
+    return all_rows, all_det, shards

@@ -29,7 +29,7 @@ class WfConfig(C.Structure):
         ("n_bands", C.c_int32), ("band_lo", C.c_int32 * MAX_BANDS), ("band_hi", C.c_int32 * MAX_BANDS),
         ("det_lo", C.c_int32), ("det_w", C.c_int32), ("noise_lo", C.c_int32), ("noise_w", C.c_int32),
         ("avg_bins", C.c_int32), ("device", C.c_int32), ("max_batch_frames", C.c_int32),
-        ("reserved", C.c_int32 * 6),
+        ("row_avg", C.c_int32), ("bin_decim", C.c_int32), ("reserved", C.c_int32 * 4),
     ]
 
 
@@ -62,6 +62,9 @@ def load_library():
         "ro_wf_destroy": (None, [vp]),
         "ro_wf_row_width": (C.c_int, [vp]),
         "ro_wf_overlap": (C.c_int, [vp]),
+        "ro_wf_out_bins": (C.c_int, [vp]),
+        "ro_wf_row_count": (sz, [vp, sz]),
+        "ro_wf_reduce_resident": (C.c_int, [vp, vp, sz, vp, P(sz), C.c_int]),
         "ro_wf_push": (C.c_int, [vp, vp, sz]),
         "ro_wf_poll": (C.c_int, [vp, vp, sz, vp, P(sz), P(u64)]),
         "ro_wf_flush": (C.c_int, [vp]),
@@ -179,7 +182,7 @@ class Waterfall:
     def __init__(self, bins: int, overlap: int, *, sample_rate: int = 48000, in_format: int = IN_INT16,
                  iq_gain: float = 0.0, iq_phase_shift: int = 0,
                  bands: Sequence[Tuple[int, int]] = (), detector: Optional[dict] = None,
-                 device: int = 0, max_batch_frames: int = 0):
+                 device: int = 0, max_batch_frames: int = 0, row_avg: int = 1, bin_decim: int = 1):
         self.lib = load_library()
         cfg = WfConfig()
         cfg.bins, cfg.overlap, cfg.sample_rate, cfg.in_format = bins, overlap, sample_rate, in_format
@@ -192,6 +195,7 @@ class Waterfall:
             cfg.noise_lo, cfg.noise_w = detector["noise_lo"], detector["noise_w"]
             cfg.avg_bins = detector["avg_bins"]
         cfg.device, cfg.max_batch_frames = device, max_batch_frames
+        cfg.row_avg, cfg.bin_decim = row_avg, bin_decim
         self.cfg = cfg
         h = C.c_void_p()
         _check(self.lib.ro_wf_create(C.byref(cfg), C.byref(h)))
@@ -200,6 +204,8 @@ class Waterfall:
         self.overlap = self.lib.ro_wf_overlap(h)
         self.hop = bins - self.overlap
         self.row_width = self.lib.ro_wf_row_width(h)
+        self.out_bins = self.lib.ro_wf_out_bins(h)
+        self.row_avg = max(1, row_avg)
         self.device = device
         self.det_on = bool(detector)
 
@@ -216,6 +222,10 @@ class Waterfall:
 
     def frame_count(self, n_samples: int) -> int:
         return int(self.lib.ro_wf_frame_count(self.h, n_samples))
+
+    def row_count(self, n_samples: int) -> int:
+        """output rows: frame_count // row_avg"""
+        return int(self.lib.ro_wf_row_count(self.h, n_samples))
 
     def _n_samples(self, iq: np.ndarray) -> int:
         if self.cfg.in_format == IN_COMPLEX64:
@@ -263,7 +273,7 @@ class Waterfall:
                      det_out: Optional[np.ndarray] = None, want_rows: bool = True):
         iq = np.ascontiguousarray(iq) if not isinstance(iq, np.ndarray) or not iq.flags.c_contiguous else iq
         ns = self._n_samples(iq)
-        F = self.frame_count(ns)
+        F = self.row_count(ns)
         if rows_out is None and want_rows:
             rows_out = np.empty((F, self.row_width), dtype=np.float32)
         if det_out is None and self.det_on:
@@ -278,8 +288,13 @@ class Waterfall:
     def process_resident(self, d_iq: int, n_samples: int, d_rows: int, d_det: Optional[int],
                          max_frames: Optional[int] = None, sync: bool = True) -> int:
         n = C.c_size_t(0)
-        mf = self.frame_count(n_samples) if max_frames is None else max_frames
+        mf = self.row_count(n_samples) if max_frames is None else max_frames
         _check(self.lib.ro_wf_process_resident(self.h, d_iq, n_samples, d_rows, d_det, mf, C.byref(n), int(sync)))
+        return n.value
+
+    def reduce_resident(self, d_rows: int, n_in: int, d_out: int, sync: bool = True) -> int:
+        n = C.c_size_t(0)
+        _check(self.lib.ro_wf_reduce_resident(self.h, d_rows, n_in, d_out, C.byref(n), int(sync)))
         return n.value
 
     def detect_resident(self, d_rows: int, n_rows: int, d_det: int, sync: bool = True):

@@ -97,6 +97,14 @@ struct ro_wf {
 	int row_width;
 	int n_sms;
 	bool det_on;
+	// extension stages (wf_reduce_kernel): R rows x D bins -> one RMS value
+	int R, D, log2d;
+	bool red_on;
+	int out_bins;                         // N / D: floats per device row handed to the detector / D2H
+	float *d_red[2];                      // batch path: reduced rows per slot
+	float *d_sred[2];                     // streaming path: reduced rows per slot
+	float *d_rscratch;                    // resident path: full rows of one chunk
+	size_t rscratch_frames;
 	KernelChoice kc;
 	int grid_cap;                         // resident CTAs for the persistent grid
 	det_kernel_t det_fn;
@@ -380,7 +388,7 @@ int launch_detect(ro_wf *h, cudaStream_t s, const float *d_rows, long long row_s
 	p.rows = d_rows;
 	p.row_stride = row_stride;
 	p.n_rows = n_rows;
-	p.bins = h->N;
+	p.bins = h->out_bins;
 	p.det_lo = h->cfg.det_lo;
 	p.det_w = h->cfg.det_w;
 	p.noise_lo = h->cfg.noise_lo;
@@ -407,6 +415,28 @@ int launch_detect(ro_wf *h, cudaStream_t s, const float *d_rows, long long row_s
 	return RO_OK;
 }
 
+// n_out groups of R full rows at d_rows (pitch N) -> n_out rows of out_bins floats at d_out
+int launch_reduce(ro_wf *h, cudaStream_t s, const float *d_rows, long long n_out, float *d_out)
+{
+	if (n_out <= 0) return RO_OK;
+	ro::ReduceParams p;
+	p.rows = d_rows;
+	p.out = d_out;
+	p.in_stride = h->N;
+	p.out_stride = h->out_bins;
+	p.n_out = n_out;
+	p.bins = h->N;
+	p.row_avg = h->R;
+	p.log2d = h->log2d;
+	long long blocks = (n_out * (h->N / 4) + 255) / 256;
+	const long long cap = (long long)h->n_sms * 8;
+	if (blocks > cap) blocks = cap;
+	ro::wf_reduce_kernel<<<(int)blocks, 256, 0, s>>>(p);
+	CU(cudaGetLastError());
+	h->launches++;
+	return RO_OK;
+}
+
 void free_all(ro_wf *h)
 {
 	if (!h) return;
@@ -416,6 +446,7 @@ void free_all(ro_wf *h)
 	for (int i = 0; i < 2; i++) {
 		cudaFree(h->d_in[i]); cudaFree(h->d_rows[i]); cudaFree(h->d_det[i]);
 		cudaFree(h->d_sin[i]); cudaFree(h->d_srows[i]); cudaFree(h->d_sdet[i]);
+		cudaFree(h->d_red[i]); cudaFree(h->d_sred[i]);
 		if (h->h_stage[i]) cudaFreeHost(h->h_stage[i]);
 		if (h->h_srows[i]) cudaFreeHost(h->h_srows[i]);
 		if (h->h_sdet[i]) cudaFreeHost(h->h_sdet[i]);
@@ -430,6 +461,7 @@ void free_all(ro_wf *h)
 	cudaFree(h->d_tw);
 	cudaFree(h->d_tw_nb);
 	cudaFree(h->d_scratch);
+	cudaFree(h->d_rscratch);
 	if (h->own_stream) cudaStreamDestroy(h->own_stream);
 	if (h->h2d_stream) cudaStreamDestroy(h->h2d_stream);
 	if (h->d2h_stream) cudaStreamDestroy(h->d2h_stream);
@@ -452,16 +484,22 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 		return fail(RO_E_INVALID, "in_format = %d", cfg->in_format);
 	if (cfg->n_bands < 0 || cfg->n_bands > RO_MAX_BANDS)
 		return fail(RO_E_INVALID, "n_bands = %d", cfg->n_bands);
+	const int R = cfg->row_avg > 0 ? cfg->row_avg : 1, D = cfg->bin_decim > 0 ? cfg->bin_decim : 1;
+	if (cfg->row_avg < 0 || R > 65536)
+		return fail(RO_E_INVALID, "row_avg = %d: must be in [1, 65536] (0 = off)", cfg->row_avg);
+	if (cfg->bin_decim < 0 || D > 128 || (D & (D - 1)))
+		return fail(RO_E_INVALID, "bin_decim = %d: must be a power of two in [1, 128] (0 = off)", cfg->bin_decim);
+	const int NO = N / D;                     // bins of a device row after decimation
 	int width = 0;
 	for (int b = 0; b < cfg->n_bands; b++) {
-		if (cfg->band_lo[b] < 0 || cfg->band_hi[b] > N || cfg->band_lo[b] >= cfg->band_hi[b])
-			return fail(RO_E_INVALID, "band %d = [%d, %d) outside [0, %d)", b, cfg->band_lo[b], cfg->band_hi[b], N);
+		if (cfg->band_lo[b] < 0 || cfg->band_hi[b] > NO || cfg->band_lo[b] >= cfg->band_hi[b])
+			return fail(RO_E_INVALID, "band %d = [%d, %d) outside [0, %d)", b, cfg->band_lo[b], cfg->band_hi[b], NO);
 		width += cfg->band_hi[b] - cfg->band_lo[b];
 	}
 	const bool det_on = cfg->det_w > 0;
 	if (det_on) {
-		if (cfg->det_lo < 0 || cfg->det_lo + cfg->det_w > N || cfg->noise_lo < 0 || cfg->noise_w < 1 ||
-		    cfg->noise_lo + cfg->noise_w > N || cfg->avg_bins < 1)
+		if (cfg->det_lo < 0 || cfg->det_lo + cfg->det_w > NO || cfg->noise_lo < 0 || cfg->noise_w < 1 ||
+		    cfg->noise_lo + cfg->noise_w > NO || cfg->avg_bins < 1)
 			return fail(RO_E_INVALID, "detector bands outside the row (det [%d,+%d) noise [%d,+%d) avg %d)",
 			            cfg->det_lo, cfg->det_w, cfg->noise_lo, cfg->noise_w, cfg->avg_bins);
 	}
@@ -483,7 +521,12 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 	h->hop = N - ov;
 	h->fmt = cfg->in_format == RO_IN_INT16 ? ro::FMT_INT16 : ro::FMT_FLOAT32;
 	h->in_bytes = h->fmt == ro::FMT_INT16 ? 4 : 8;
-	h->row_width = cfg->n_bands ? width : N;
+	h->R = R;
+	h->D = D;
+	h->log2d = ro::ilog2(D);
+	h->red_on = R > 1 || D > 1;
+	h->out_bins = NO;
+	h->row_width = cfg->n_bands ? width : NO;
 	h->det_on = det_on;
 	if (!choose_kernel(h->log2n, h->fmt, &h->kc)) { free_all(h); return fail(RO_E_INVALID, "no kernel for bins = %d", N); }
 
@@ -587,6 +630,8 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 		CUH(cudaEventCreateWithFlags(&h->ev_slot[i], cudaEventDisableTiming));
 	}
 	h->batch_frames = cfg->max_batch_frames > 0 ? (size_t)cfg->max_batch_frames : 64;
+	// a batch is a whole number of row groups
+	h->batch_frames = ((h->batch_frames + (size_t)R - 1) / (size_t)R) * (size_t)R;
 	*out = h;
 	return RO_OK;
 }
@@ -595,11 +640,17 @@ extern "C" void ro_wf_destroy(ro_wf *h) { free_all(h); }
 
 extern "C" int ro_wf_row_width(const ro_wf *h) { return h ? h->row_width : 0; }
 extern "C" int ro_wf_overlap(const ro_wf *h) { return h ? h->overlap : 0; }
+extern "C" int ro_wf_out_bins(const ro_wf *h) { return h ? h->out_bins : 0; }
 
 extern "C" size_t ro_wf_frame_count(const ro_wf *h, size_t n_samples)
 {
 	if (!h || n_samples < (size_t)h->N) return 0;
 	return (n_samples - (size_t)h->N) / (size_t)h->hop + 1;
+}
+
+extern "C" size_t ro_wf_row_count(const ro_wf *h, size_t n_samples)
+{
+	return h ? ro_wf_frame_count(h, n_samples) / (size_t)h->R : 0;
 }
 
 extern "C" int ro_wf_set_stream(ro_wf *h, void *cuda_stream)
@@ -661,13 +712,47 @@ extern "C" int ro_wf_process_resident(ro_wf *h, const void *d_iq, size_t n_sampl
 	if (h->cfg.in_format == RO_IN_COMPLEX64)
 		return fail(RO_E_INVALID, "device-resident input must be int16 or float32");
 	CU(cudaSetDevice(h->cfg.device));
-	size_t F = ro_wf_frame_count(h, n_samples);
+	size_t F = ro_wf_row_count(h, n_samples);
 	if (F > max_frames) F = max_frames;
 	if (n_frames) *n_frames = F;
 	cudaStream_t s = batch_stream(h);
-	int rc = launch_fft(h, s, d_iq, d_rows, h->N, (long long)F);
+	int rc;
+	if (!h->red_on) {
+		rc = launch_fft(h, s, d_iq, d_rows, h->N, (long long)F);
+		if (rc) return rc;
+	} else {
+		// full rows of one chunk of row groups go through a scratch (about 256 MiB), then the reduction
+		if (!h->d_rscratch) {
+			size_t groups = ((size_t)256 << 20) / (sizeof(float) * (size_t)h->N * (size_t)h->R);
+			if (groups < 1) groups = 1;
+			h->rscratch_frames = groups * (size_t)h->R;
+			CU(cudaMalloc((void **)&h->d_rscratch, h->rscratch_frames * (size_t)h->N * sizeof(float)));
+		}
+		const size_t gpc = h->rscratch_frames / (size_t)h->R;       // groups per chunk
+		for (size_t g0 = 0; g0 < F; g0 += gpc) {
+			const size_t ng = std::min(gpc, F - g0);
+			const unsigned char *src = (const unsigned char *)d_iq + g0 * (size_t)h->R * (size_t)h->hop * (size_t)h->in_bytes;
+			rc = launch_fft(h, s, src, h->d_rscratch, h->N, (long long)(ng * (size_t)h->R));
+			if (rc) return rc;
+			rc = launch_reduce(h, s, h->d_rscratch, (long long)ng, d_rows + g0 * (size_t)h->out_bins);
+			if (rc) return rc;
+		}
+	}
+	rc = launch_detect(h, s, d_rows, h->out_bins, (long long)F, d_det);
 	if (rc) return rc;
-	rc = launch_detect(h, s, d_rows, h->N, (long long)F, d_det);
+	if (sync) CU(cudaStreamSynchronize(s));
+	return RO_OK;
+}
+
+extern "C" int ro_wf_reduce_resident(ro_wf *h, const float *d_rows, size_t n_in, float *d_out,
+                                     size_t *n_out, int sync)
+{
+	if (!h || !d_rows || !d_out) return fail(RO_E_INVALID, "ro_wf_reduce_resident: null argument");
+	CU(cudaSetDevice(h->cfg.device));
+	const size_t n = n_in / (size_t)h->R;
+	if (n_out) *n_out = n;
+	cudaStream_t s = batch_stream(h);
+	int rc = launch_reduce(h, s, d_rows, (long long)n, d_out);
 	if (rc) return rc;
 	if (sync) CU(cudaStreamSynchronize(s));
 	return RO_OK;
@@ -680,7 +765,7 @@ extern "C" int ro_wf_detect_resident(ro_wf *h, const float *d_rows, size_t n_row
 	if (!h->det_on) return fail(RO_E_STATE, "detector not configured (det_w = 0)");
 	CU(cudaSetDevice(h->cfg.device));
 	cudaStream_t s = batch_stream(h);
-	int rc = launch_detect(h, s, d_rows, h->N, (long long)n_rows, d_det);
+	int rc = launch_detect(h, s, d_rows, h->out_bins, (long long)n_rows, d_det);
 	if (rc) return rc;
 	if (sync) CU(cudaStreamSynchronize(s));
 	return RO_OK;
@@ -693,14 +778,14 @@ int copy_rows_out(ro_wf *h, cudaStream_t s, float *dst, const float *d_rows, siz
 {
 	if (!dst || n == 0) return RO_OK;
 	if (h->cfg.n_bands == 0) {
-		CU(cudaMemcpyAsync(dst, d_rows, sizeof(float) * (size_t)h->N * n, cudaMemcpyDeviceToHost, s));
+		CU(cudaMemcpyAsync(dst, d_rows, sizeof(float) * (size_t)h->out_bins * n, cudaMemcpyDeviceToHost, s));
 		return RO_OK;
 	}
 	size_t off = 0;
 	for (int b = 0; b < h->cfg.n_bands; b++) {
 		const size_t w = (size_t)(h->cfg.band_hi[b] - h->cfg.band_lo[b]);
 		CU(cudaMemcpy2DAsync(dst + off, sizeof(float) * (size_t)h->row_width,
-		                     d_rows + h->cfg.band_lo[b], sizeof(float) * (size_t)h->N,
+		                     d_rows + h->cfg.band_lo[b], sizeof(float) * (size_t)h->out_bins,
 		                     sizeof(float) * w, n, cudaMemcpyDeviceToHost, s));
 		off += w;
 	}
@@ -714,6 +799,7 @@ int ensure_batch_buffers(ro_wf *h)
 	size_t cf = ((size_t)256 << 20) / (sizeof(float) * (size_t)h->N);
 	if (cf < 1) cf = 1;
 	if (cf > 8192) cf = 8192;
+	cf = std::max((size_t)1, cf / (size_t)h->R) * (size_t)h->R;       // whole row groups
 	h->chunk_frames = cf;
 	h->d_in_bytes = ((cf - 1) * (size_t)h->hop + (size_t)h->N) * (size_t)h->in_bytes;
 	h->d_rows_bytes = cf * (size_t)h->N * sizeof(float);
@@ -721,6 +807,7 @@ int ensure_batch_buffers(ro_wf *h)
 		CU(cudaMalloc(&h->d_in[i], h->d_in_bytes));
 		CU(cudaMalloc((void **)&h->d_rows[i], h->d_rows_bytes));
 		CU(cudaMalloc((void **)&h->d_det[i], sizeof(ro_det_rec) * cf));
+		if (h->red_on) CU(cudaMalloc((void **)&h->d_red[i], (cf / (size_t)h->R) * (size_t)h->out_bins * sizeof(float)));
 	}
 	return RO_OK;
 }
@@ -739,10 +826,12 @@ extern "C" int ro_wf_process_host(ro_wf *h, const void *iq, size_t n_samples,
 {
 	if (!h || !iq) return fail(RO_E_INVALID, "ro_wf_process_host: null argument");
 	CU(cudaSetDevice(h->cfg.device));
-	size_t F = ro_wf_frame_count(h, n_samples);
-	if (F > max_frames) F = max_frames;
-	if (n_frames) *n_frames = F;
-	if (F == 0) return RO_OK;
+	const size_t R = (size_t)h->R;
+	size_t G = ro_wf_row_count(h, n_samples);        // output rows
+	if (G > max_frames) G = max_frames;
+	if (n_frames) *n_frames = G;
+	if (G == 0) return RO_OK;
+	const size_t F = G * R;                          // frames transformed
 	int rc = ensure_batch_buffers(h);
 	if (rc) return rc;
 
@@ -772,14 +861,21 @@ extern "C" int ro_wf_process_host(ro_wf *h, const void *iq, size_t n_samples,
 		if (c >= 2) CU(cudaStreamWaitEvent(sc, h->ev_d2h[s], 0));
 		rc = launch_fft(h, sc, h->d_in[s], h->d_rows[s], h->N, (long long)nf);
 		if (rc) return rc;
-		rc = launch_detect(h, sc, h->d_rows[s], h->N, (long long)nf, det ? h->d_det[s] : NULL);
+		const size_t ng = nf / R, g0 = f0 / R;       // chunk_frames is a multiple of R
+		const float *d_out = h->d_rows[s];
+		if (h->red_on) {
+			rc = launch_reduce(h, sc, h->d_rows[s], (long long)ng, h->d_red[s]);
+			if (rc) return rc;
+			d_out = h->d_red[s];
+		}
+		rc = launch_detect(h, sc, d_out, h->out_bins, (long long)ng, det ? h->d_det[s] : NULL);
 		if (rc) return rc;
 		CU(cudaEventRecord(h->ev_comp[s], sc));
 		CU(cudaStreamWaitEvent(h->d2h_stream, h->ev_comp[s], 0));
-		rc = copy_rows_out(h, h->d2h_stream, rows ? rows + f0 * (size_t)h->row_width : NULL, h->d_rows[s], nf);
+		rc = copy_rows_out(h, h->d2h_stream, rows ? rows + g0 * (size_t)h->row_width : NULL, d_out, ng);
 		if (rc) return rc;
 		if (det && h->det_on)
-			CU(cudaMemcpyAsync(det + f0, h->d_det[s], sizeof(ro_det_rec) * nf, cudaMemcpyDeviceToHost, h->d2h_stream));
+			CU(cudaMemcpyAsync(det + g0, h->d_det[s], sizeof(ro_det_rec) * ng, cudaMemcpyDeviceToHost, h->d2h_stream));
 		CU(cudaEventRecord(h->ev_d2h[s], h->d2h_stream));
 	}
 	CU(cudaStreamSynchronize(h->d2h_stream));
@@ -798,13 +894,17 @@ int ensure_stream_buffers(ro_wf *h)
 	if (h->h_stage[0]) return RO_OK;
 	const size_t N = (size_t)h->N, hop = (size_t)h->hop;
 	h->stage_cap = h->batch_frames * hop + N;
-	h->slot_rows_cap = h->stage_cap / hop + 2;
+	// up to R-1 frames wait on the device for their row group to complete: room for them in the
+	// carry and in the row slots
+	const size_t held = ((size_t)h->R - 1) * hop;
+	h->slot_rows_cap = h->stage_cap / hop + 2 + ((size_t)h->R - 1);
 	const size_t host_in_bytes = h->stage_cap * (size_t)h->in_bytes;
 	for (int i = 0; i < 2; i++) {
 		CU(cudaMallocHost((void **)&h->h_stage[i], host_in_bytes));
-		CU(cudaMalloc(&h->d_sin[i], (h->stage_cap + N) * (size_t)h->in_bytes));
+		CU(cudaMalloc(&h->d_sin[i], (h->stage_cap + N + held) * (size_t)h->in_bytes));
 		CU(cudaMalloc((void **)&h->d_srows[i], h->slot_rows_cap * N * sizeof(float)));
 		CU(cudaMalloc((void **)&h->d_sdet[i], h->slot_rows_cap * sizeof(ro_det_rec)));
+		if (h->red_on) CU(cudaMalloc((void **)&h->d_sred[i], (h->slot_rows_cap / (size_t)h->R + 1) * (size_t)h->out_bins * sizeof(float)));
 		CU(cudaMallocHost((void **)&h->h_srows[i], h->slot_rows_cap * (size_t)h->row_width * sizeof(float)));
 		CU(cudaMallocHost((void **)&h->h_sdet[i], h->slot_rows_cap * sizeof(ro_det_rec)));
 	}
@@ -825,7 +925,8 @@ int retire(ro_wf *h, Pending *p)
 int submit(ro_wf *h)
 {
 	const size_t total = h->carry + h->staged;
-	const size_t F = ro_wf_frame_count(h, total);
+	const size_t G = ro_wf_row_count(h, total);           // whole row groups only; the rest stays staged
+	const size_t F = G * (size_t)h->R;
 	if (F == 0) return RO_OK;
 	const int s = h->cur;
 	cudaStream_t st = h->own_stream;
@@ -835,12 +936,18 @@ int submit(ro_wf *h)
 		                   h->staged * (size_t)h->in_bytes, cudaMemcpyHostToDevice, st));
 	int rc = launch_fft(h, st, d_in, h->d_srows[s], h->N, (long long)F);
 	if (rc) return rc;
-	rc = launch_detect(h, st, h->d_srows[s], h->N, (long long)F, h->d_sdet[s]);
+	const float *d_out = h->d_srows[s];
+	if (h->red_on) {
+		rc = launch_reduce(h, st, h->d_srows[s], (long long)G, h->d_sred[s]);
+		if (rc) return rc;
+		d_out = h->d_sred[s];
+	}
+	rc = launch_detect(h, st, d_out, h->out_bins, (long long)G, h->d_sdet[s]);
 	if (rc) return rc;
-	rc = copy_rows_out(h, st, h->h_srows[s], h->d_srows[s], F);
+	rc = copy_rows_out(h, st, h->h_srows[s], d_out, G);
 	if (rc) return rc;
 	if (h->det_on)
-		CU(cudaMemcpyAsync(h->h_sdet[s], h->d_sdet[s], sizeof(ro_det_rec) * F, cudaMemcpyDeviceToHost, st));
+		CU(cudaMemcpyAsync(h->h_sdet[s], h->d_sdet[s], sizeof(ro_det_rec) * G, cudaMemcpyDeviceToHost, st));
 	const size_t left = total - F * (size_t)h->hop;       // overlap carried to the next frame
 	if (left)
 		CU(cudaMemcpyAsync(h->d_sin[s ^ 1], d_in + F * (size_t)h->hop * (size_t)h->in_bytes,
@@ -850,12 +957,12 @@ int submit(ro_wf *h)
 	Pending *p = new (std::nothrow) Pending();
 	if (!p) return fail(RO_E_NOMEM, "out of memory");
 	p->first_row = h->next_row;
-	p->n_rows = F;
+	p->n_rows = G;
 	p->consumed = 0;
 	p->slot = s;
 	p->done = 0;
 	h->pending.push_back(p);
-	h->next_row += F;
+	h->next_row += G;
 	h->carry = left;
 	h->staged = 0;
 	h->cur = s ^ 1;

@@ -167,6 +167,66 @@ wf_fft_kernel(const WfParams p)
 }
 
 // ---------------------------------------------------------------------------
+// Row reduction (extension, default off): |X|^2, accumulate `row_avg` consecutive
+// rows, decimate `bin_decim` adjacent bins, back to amplitude:
+//     out[j][i] = sqrt( sum_{r<R} sum_{d<D} rows[j*R + r][i*D + d]^2 / (R*D) )
+// The reference has neither stage (its row rate is set by
+// `overlap` alone and its only bin reduction is the recorder's band crop); this
+// is the "|X|^2 + row-accumulate + bin-decimate" stage BASELINE.json's north_star
+// names, behind the config keys row_avg / bin_decim whose default 1/1 keeps the
+// reference's rows bit for bit (the stage is then not launched at all).
+// HBM-bound: 4*N bytes read per input row, 4*N/(R*D) written.  One thread owns
+// four adjacent input bins (128-bit coalesced loads), sums their squares over the
+// R rows of a group in row order, then D/4 adjacent lanes combine by shuffles.
+// ---------------------------------------------------------------------------
+struct ReduceParams {
+	const float *rows;        // [n_out*R][in_stride]
+	float       *out;         // [n_out][out_stride]
+	long long    in_stride, out_stride;
+	long long    n_out;       // output rows
+	int          bins;        // N, a multiple of 4*32
+	int          row_avg;     // R >= 1
+	int          log2d;       // D = 1 << log2d, D <= 128
+};
+
+__global__ void __launch_bounds__(256)
+wf_reduce_kernel(const ReduceParams p)
+{
+	const int quads = p.bins >> 2;                     // float4 columns per row
+	const long long total = p.n_out * quads;
+	const int D = 1 << p.log2d;
+	const float scale = 1.0f / ((float)p.row_avg * (float)D);
+	for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+	     idx += (long long)gridDim.x * blockDim.x) {
+		const long long j = idx / quads;
+		const int q = (int)(idx - j * quads);
+		const float4 *src = reinterpret_cast<const float4 *>(p.rows + j * p.row_avg * p.in_stride) + q;
+		float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+		for (int r = 0; r < p.row_avg; r++) {
+			const float4 x = __ldg(src);
+			acc.x = fmaf(x.x, x.x, acc.x);
+			acc.y = fmaf(x.y, x.y, acc.y);
+			acc.z = fmaf(x.z, x.z, acc.z);
+			acc.w = fmaf(x.w, x.w, acc.w);
+			src = reinterpret_cast<const float4 *>(reinterpret_cast<const float *>(src) + p.in_stride);
+		}
+		float *dst = p.out + j * p.out_stride;
+		if (D == 1) {
+			*reinterpret_cast<float4 *>(dst + 4 * q) = make_float4(sqrtf(acc.x * scale), sqrtf(acc.y * scale),
+			                                                     sqrtf(acc.z * scale), sqrtf(acc.w * scale));
+		} else if (D == 2) {
+			*reinterpret_cast<float2 *>(dst + 2 * q) = make_float2(sqrtf((acc.x + acc.y) * scale), sqrtf((acc.z + acc.w) * scale));
+		} else {
+			// quads is a multiple of 32 and idx advances by a multiple of 32: the D/4 lanes of a group
+			// sit in one warp, all 32 lanes are in the loop together
+			float v = (acc.x + acc.y) + (acc.z + acc.w);
+			for (int o = 1; o < (D >> 2); o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+			if ((q & ((D >> 2) - 1)) == 0) dst[q >> (p.log2d - 2)] = sqrtf(v * scale);
+		}
+	}
+}
+
+// ---------------------------------------------------------------------------
 // Detector: one warp per row.
 // ---------------------------------------------------------------------------
 struct DetParams {
