@@ -40,6 +40,9 @@ extern "C" {
 
 #define RO_MAX_BANDS       4
 
+#define RO_PREC_FP32       0
+#define RO_PREC_FP64       1
+
 typedef struct ro_wf ro_wf;   /* opaque: one stream on one GPU */
 
 /* Configuration.  bins/overlap/iq_gain/iq_phase_shift carry the meaning of the
@@ -68,7 +71,11 @@ typedef struct ro_wf_config {
 	 * frame.  Bands and detector bins then index the REDUCED row (bins / bin_decim wide). */
 	int32_t row_avg;                 /* rows accumulated per output row, >= 1                      */
 	int32_t bin_decim;               /* adjacent bins per output bin: power of two, 1 .. 128       */
-	int32_t reserved[4];
+	/* 0 = packed FP32 transform (the fast path; rows within 1e-3 dB of the reference's);
+	 * 1 = FP64 transform and magnitude like the reference's FFTW path (src/FFTBackend.cpp:117-120,
+	 * src/WaterfallBackend.cpp:492-505): rows within 1e-5 relative in linear power on every bin. */
+	int32_t precision;
+	int32_t reserved[3];
 } ro_wf_config;
 
 /* Per-row detector statistics: what BolidRecorder::update computes before its

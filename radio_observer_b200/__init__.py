@@ -7,7 +7,7 @@ libro_cuda.so and a B200.
 """
 from .capi import (  # noqa: F401
     RoError, WfConfig, DetRec, Waterfall, load_library, library_path,
-    window_table, twiddle_table, IN_INT16, IN_FLOAT32, IN_COMPLEX64,
+    window_table, twiddle_table, IN_INT16, IN_FLOAT32, IN_COMPLEX64, PREC_FP32, PREC_FP64,
 )
 
 from . import archive  # noqa: F401,E402  (time-sharded archive reprocessing, host-side trigger state machine)
@@ -15,5 +15,5 @@ from . import archive  # noqa: F401,E402  (time-sharded archive reprocessing, ho
 __all__ = [
     "archive",
     "RoError", "WfConfig", "DetRec", "Waterfall", "load_library", "library_path",
-    "window_table", "twiddle_table", "IN_INT16", "IN_FLOAT32", "IN_COMPLEX64",
+    "window_table", "twiddle_table", "IN_INT16", "IN_FLOAT32", "IN_COMPLEX64", "PREC_FP32", "PREC_FP64",
 ]

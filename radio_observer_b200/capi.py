@@ -12,6 +12,7 @@ from typing import Optional, Sequence, Tuple
 
 import numpy as np
 
+PREC_FP32, PREC_FP64 = 0, 1
 IN_INT16, IN_FLOAT32, IN_COMPLEX64 = 0, 1, 2
 MAX_BANDS = 4
 
@@ -29,7 +30,8 @@ class WfConfig(C.Structure):
         ("n_bands", C.c_int32), ("band_lo", C.c_int32 * MAX_BANDS), ("band_hi", C.c_int32 * MAX_BANDS),
         ("det_lo", C.c_int32), ("det_w", C.c_int32), ("noise_lo", C.c_int32), ("noise_w", C.c_int32),
         ("avg_bins", C.c_int32), ("device", C.c_int32), ("max_batch_frames", C.c_int32),
-        ("row_avg", C.c_int32), ("bin_decim", C.c_int32), ("reserved", C.c_int32 * 4),
+        ("row_avg", C.c_int32), ("bin_decim", C.c_int32), ("precision", C.c_int32),
+        ("reserved", C.c_int32 * 3),
     ]
 
 
@@ -182,7 +184,8 @@ class Waterfall:
     def __init__(self, bins: int, overlap: int, *, sample_rate: int = 48000, in_format: int = IN_INT16,
                  iq_gain: float = 0.0, iq_phase_shift: int = 0,
                  bands: Sequence[Tuple[int, int]] = (), detector: Optional[dict] = None,
-                 device: int = 0, max_batch_frames: int = 0, row_avg: int = 1, bin_decim: int = 1):
+                 device: int = 0, max_batch_frames: int = 0, row_avg: int = 1, bin_decim: int = 1,
+                 precision: int = 0):
         self.lib = load_library()
         cfg = WfConfig()
         cfg.bins, cfg.overlap, cfg.sample_rate, cfg.in_format = bins, overlap, sample_rate, in_format
@@ -195,7 +198,7 @@ class Waterfall:
             cfg.noise_lo, cfg.noise_w = detector["noise_lo"], detector["noise_w"]
             cfg.avg_bins = detector["avg_bins"]
         cfg.device, cfg.max_batch_frames = device, max_batch_frames
-        cfg.row_avg, cfg.bin_decim = row_avg, bin_decim
+        cfg.row_avg, cfg.bin_decim, cfg.precision = row_avg, bin_decim, precision
         self.cfg = cfg
         h = C.c_void_p()
         _check(self.lib.ro_wf_create(C.byref(cfg), C.byref(h)))

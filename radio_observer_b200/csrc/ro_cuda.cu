@@ -18,6 +18,7 @@
 #include "../../include/ro_cuda.h"
 #include "ro_kernels.cuh"
 #include "ro_v2.h"
+#include "ro_fft64.cuh"
 
 namespace {
 
@@ -105,6 +106,11 @@ struct ro_wf {
 	float *d_sred[2];                     // streaming path: reduced rows per slot
 	float *d_rscratch;                    // resident path: full rows of one chunk
 	size_t rscratch_frames;
+	// cfg.precision = 1: the reference's arithmetic in double (ro_fft64.cuh)
+	bool fp64;
+	double2 *d_tw64;                      // N/2 entries exp(-2*pi*i*j/N)
+	double2 *d_x64;                       // [x64_frames][N]
+	long long x64_frames;
 	KernelChoice kc;
 	int grid_cap;                         // resident CTAs for the persistent grid
 	det_kernel_t det_fn;
@@ -302,6 +308,46 @@ int launch_fft(ro_wf *h, cudaStream_t s, const void *d_iq, float *d_rows, long l
                long long n_frames)
 {
 	if (n_frames <= 0) return RO_OK;
+	if (h->fp64) {
+		cudaEvent_t e0 = 0, e1 = 0;
+		if (h->profiling) {
+			int rc = get_event(h, &e0); if (rc) return rc;
+			rc = get_event(h, &e1); if (rc) return rc;
+			CU(cudaEventRecord(e0, s));
+		}
+		const int blocks = h->n_sms * 8;
+		for (long long f0 = 0; f0 < n_frames; f0 += h->x64_frames) {
+			ro::Wf64Params p;
+			p.iq = (const unsigned char *)d_iq + f0 * h->hop * h->in_bytes;
+			p.window = h->d_window;
+			p.tw = h->d_tw64;
+			p.x = h->d_x64;
+			p.rows = d_rows + f0 * row_stride;
+			p.n_frames = std::min<long long>(h->x64_frames, n_frames - f0);
+			p.hop = h->hop;
+			p.row_stride = row_stride;
+			p.iq_gain = h->cfg.iq_gain;
+			p.log2n = h->log2n;
+			p.stage = 0;
+			if (h->fmt == ro::FMT_FLOAT32) ro::wf64_load_kernel<true><<<blocks, 256, 0, s>>>(p);
+			else ro::wf64_load_kernel<false><<<blocks, 256, 0, s>>>(p);
+			ro::wf64_block_kernel<<<blocks, 256, 0, s>>>(p);
+			h->launches += 2;
+			for (int st = ro::WF64_LOG2B + 1; st <= h->log2n; st++) {
+				p.stage = st;
+				ro::wf64_stage_kernel<<<blocks, 256, 0, s>>>(p);
+				h->launches++;
+			}
+			ro::wf64_mag_kernel<<<blocks, 256, 0, s>>>(p);
+			h->launches++;
+			CU(cudaGetLastError());
+		}
+		if (h->profiling) {
+			CU(cudaEventRecord(e1, s));
+			h->ev_used[0].push_back(std::make_pair(e0, e1));
+		}
+		return RO_OK;
+	}
 	if (h->split_ok) {
 		cudaEvent_t e0 = 0, e1 = 0;
 		if (h->profiling) {
@@ -462,6 +508,8 @@ void free_all(ro_wf *h)
 	cudaFree(h->d_tw_nb);
 	cudaFree(h->d_scratch);
 	cudaFree(h->d_rscratch);
+	cudaFree(h->d_tw64);
+	cudaFree(h->d_x64);
 	if (h->own_stream) cudaStreamDestroy(h->own_stream);
 	if (h->h2d_stream) cudaStreamDestroy(h->h2d_stream);
 	if (h->d2h_stream) cudaStreamDestroy(h->d2h_stream);
@@ -489,6 +537,8 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 		return fail(RO_E_INVALID, "row_avg = %d: must be in [1, 65536] (0 = off)", cfg->row_avg);
 	if (cfg->bin_decim < 0 || D > 128 || (D & (D - 1)))
 		return fail(RO_E_INVALID, "bin_decim = %d: must be a power of two in [1, 128] (0 = off)", cfg->bin_decim);
+	if (cfg->precision != RO_PREC_FP32 && cfg->precision != RO_PREC_FP64)
+		return fail(RO_E_INVALID, "precision = %d: 0 (FP32) or 1 (FP64)", cfg->precision);
 	const int NO = N / D;                     // bins of a device row after decimation
 	int width = 0;
 	for (int b = 0; b < cfg->n_bands; b++) {
@@ -579,6 +629,20 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 				h->v2_grid_cap[st] = occ2 * h->n_sms;
 			}
 		}
+	}
+	h->fp64 = cfg->precision == RO_PREC_FP64;
+	if (h->fp64) {
+		std::vector<double> tw64((size_t)N);                       // N/2 complex entries
+		const long double two_pi = 8.0L * atanl(1.0L);
+		for (int j = 0; j < N / 2; j++) {
+			const long double a = two_pi * (long double)j / (long double)N;
+			tw64[2 * (size_t)j] = (double)cosl(a);
+			tw64[2 * (size_t)j + 1] = (double)-sinl(a);
+		}
+		CUH(cudaMalloc((void **)&h->d_tw64, sizeof(double) * (size_t)N));
+		CUH(cudaMemcpy(h->d_tw64, tw64.data(), sizeof(double) * (size_t)N, cudaMemcpyHostToDevice));
+		h->x64_frames = std::max<long long>(1, ((long long)256 << 20) / ((long long)sizeof(double2) * N));
+		CUH(cudaMalloc((void **)&h->d_x64, sizeof(double2) * (size_t)N * (size_t)h->x64_frames));
 	}
 	h->split_ok = false;
 	// passes 2 and 3 chained (bits 1, 2): +19 % on the 16k kernel (B200, 21.0 -> 25.0 M frames/s);

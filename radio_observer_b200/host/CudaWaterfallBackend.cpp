@@ -21,11 +21,12 @@
 #include <cstring>
 
 CudaWaterfallBackend::CudaWaterfallBackend(int bins, int overlap, std::string origin,
-                                           int device, int batchFrames) :
+                                           int device, int batchFrames, int precision) :
 	WaterfallBackend(bins, overlap, origin),
 	overlap_(overlap),
 	device_(device),
 	batchFrames_(batchFrames < 1 ? 1 : batchFrames),
+	precision_(precision),
 	iqGain_(0), iqPhaseShift_(0),
 	wf_(NULL), failed_(false),
 	fill_(0),
@@ -83,6 +84,7 @@ void CudaWaterfallBackend::startStream(StreamInfo info)
 	cfg.n_bands = 0;                          // recorders slice the full row themselves
 	cfg.device = device_;
 	cfg.max_batch_frames = batchFrames_;
+	cfg.precision = precision_;
 	if (ro_wf_create(&cfg, &wf_) != RO_OK) {
 		wf_ = NULL;
 		fail("ro_wf_create");
@@ -180,7 +182,7 @@ void CudaWaterfallBackend::endStream()
 Ref<DIObject> CudaWaterfallBackend::make(Ref<DynObject> config, Ref<DIObject> parent)
 {
 	// the keys of WaterfallBackend::make (src/WaterfallBackend.cpp:620-644) with
-	// the same defaults, plus cuda_device / cuda_batch_frames
+	// the same defaults, plus cuda_device / cuda_batch_frames / cuda_precision
 	int bins      = config->getStrInt("bins",        32768);
 	int overlap   = config->getStrInt("overlap",         0);
 	string origin = config->getStrString("origin", "debug");
@@ -188,7 +190,8 @@ Ref<DIObject> CudaWaterfallBackend::make(Ref<DynObject> config, Ref<DIObject> pa
 	Ref<CudaWaterfallBackend> backend = new CudaWaterfallBackend(
 		bins, overlap, origin,
 		config->getStrInt("cuda_device", 0),
-		config->getStrInt("cuda_batch_frames", 1)
+		config->getStrInt("cuda_batch_frames", 1),
+		config->getStrInt("cuda_precision", 0)
 	);
 
 	backend->setMetadataPath(

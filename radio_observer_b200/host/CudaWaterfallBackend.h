@@ -12,7 +12,7 @@
  *
  * Selecting it is one string in the JSON config:  "factory": "waterfall_cuda"
  * (same keys as "waterfall", src/WaterfallBackend.cpp:620-644, plus the optional
- * keys cuda_device (0) and cuda_batch_frames (1)).
+ * keys cuda_device (0), cuda_batch_frames (1) and cuda_precision (0 = FP32, 1 = FP64)).
  */
 #ifndef CUDA_WATERFALL_BACKEND_H
 #define CUDA_WATERFALL_BACKEND_H
@@ -35,6 +35,7 @@ private:
 	int     overlap_;          // clamped like FFTBackend::FFTBackend (src/FFTBackend.cpp:108-109)
 	int     device_;
 	int     batchFrames_;      // frames submitted per kernel launch; 1 = lowest latency
+	int     precision_;        // 0 = packed FP32 transform, 1 = FP64 like the reference's FFTW path
 	double  iqGain_;
 	int     iqPhaseShift_;
 
@@ -56,7 +57,7 @@ private:
 	void fail(const char *what);
 
 public:
-	CudaWaterfallBackend(int bins, int overlap, std::string origin, int device, int batchFrames);
+	CudaWaterfallBackend(int bins, int overlap, std::string origin, int device, int batchFrames, int precision = 0);
 	virtual ~CudaWaterfallBackend();
 
 

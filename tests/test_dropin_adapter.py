@@ -154,5 +154,46 @@ def test_cuda_backend_is_a_drop_in(name, batch):
         shutil.rmtree(tmp, ignore_errors=True)
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["n2048", "c2b_16k"])
+def test_cuda_backend_fp64_reproduces_the_stock_backend(name):
+    """cuda_precision = 1: the reference's Pipeline with the CUDA backend in double precision gives the
+    stock backend's rows to the last float ulp, hence the same detector statistics, events and files."""
+    if not (os.path.exists(REF_BIN) and os.path.exists(CUDA_BIN)):
+        pytest.fail("prebuilt binaries missing: run __graft_entry__.build() in the build container")
+    g = load_golden(name)
+    tmp = tempfile.mkdtemp(prefix="ro_dropin64_")
+    try:
+        ref = run_pipeline(REF_BIN, g, "waterfall", tmp)
+        for attempt in range(6):            # the reference's gmtime race, see above
+            got = run_pipeline(CUDA_BIN, g, "waterfall_cuda", tmp, {"cuda_batch_frames": 1, "cuda_precision": 1})
+            if sorted(got["fits"]) == sorted(ref["fits"]):
+                break
+            shutil.rmtree(os.path.join(tmp, "waterfall_cuda"))
+        assert got["rows"].shape == ref["rows"].shape
+        ulp = np.spacing(np.abs(ref["rows"]))
+        assert (np.abs(got["rows"] - ref["rows"]) <= ulp).all()
+        same = float((got["rows"] == ref["rows"]).mean())
+        print("[dropin fp64] %s: %.4f %% of pixels bit-identical, the rest one ulp apart" % (name, 100 * same))
+        assert same > 0.99
+        for k in ("mark", "sec", "usec", "rawmark"):
+            assert np.array_equal(got["info"][k], ref["info"][k])
+        # detector statistics of the unmodified BolidRecorder: identical unless a one-ulp pixel is involved
+        assert np.array_equal(got["npa"]["peakfreq"], ref["npa"]["peakfreq"])
+        assert np.allclose(got["npa"]["noise"], ref["npa"]["noise"], rtol=2e-7, atol=0)
+        assert np.allclose(got["npa"]["mag"], ref["npa"]["mag"], rtol=2e-7, atol=0)
+        assert got["bolid"].strip().splitlines().__len__() == ref["bolid"].strip().splitlines().__len__() >= 1
+        for e, q in zip(ref["bolid"].strip().splitlines(), got["bolid"].strip().splitlines()):
+            e, q = e.split(";"), q.split(";")
+            assert e[1] == q[1] and e[3:] == q[3:]          # peak frequency, band, start/end samples
+        assert sorted(got["fits"]) == sorted(ref["fits"])
+        for fn in ref["fits"]:
+            a, b = ref["fits"][fn], got["fits"][fn]
+            assert a["shape"] == b["shape"] and a["cards"] == b["cards"], fn
+            assert (np.abs(a["data"].astype(np.float64) - b["data"]) <= np.spacing(np.abs(a["data"]))).all(), fn
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
 def ref_df(g):
     return g["meta"]["sample_rate"] / g["meta"]["bins"]
