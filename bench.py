@@ -376,12 +376,12 @@ def main():
             traffic = None
     flops = 5.0 * BINS * math.log2(BINS) * F
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "kernel": "wf_fft2_kernel<14,32,16,STAGE> (packed f32x2, TMA-staged ring)", "kernel_ms": fft_ms,
+                "traffic": traffic, "kernel": "wf_fft2_kernel<14,32,16,STAGED> (packed f32x2 DIT butterflies, TMA-staged ring, chained load bursts)", "kernel_ms": fft_ms,
                 "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
                 "fft_tflops_5NlogN": flops / (fft_ms * 1e-3) / 1e12,
                 "detector_kernel_ms": kms[1] / max(1, kn[1]),
-                "fp32_roof": {"lane_ops_per_frame": 1877 * 512, "fma_pipe_floor_cycles_per_frame": 7508,
-                              "note": "FMA-pipe floor (128 lanes/clk/SM, profiles/r01_microbench_pipe_rates.txt) = 38.8 M frames/s = 0.485 of HBM peak at 20 B/sample"},
+                "fp32_roof": {"lane_ops_per_frame": 1698 * 512, "fma_pipe_floor_cycles_per_frame": 6792,
+                              "note": "FMA-pipe floor of the kernel's own instruction mix (812 packed + 74 scalar FP instructions per thread and frame, 128 lanes/clk/SM, profiles/r01_microbench_pipe_rates.txt) = 42.8 M frames/s = 0.537 of HBM peak at 20 B/sample"},
                 "note": "75% overlap: 280 flop/sample puts this shape past the FP32 ridge; the binding roof is the FMA pipe, not HBM; see DESIGN.md section 4"}
 
     # ---- end to end through the host API: pinned host in, bands + detector records out ----
