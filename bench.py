@@ -253,6 +253,15 @@ def main():
     ap.add_argument("--log2-samples", type=int, default=28, help="complex samples per GPU per step (2^k)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    # The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version
+    # banner from C on the first collective): keep the real stdout aside for the result line and point
+    # fd 1 at stderr for everything else.
+    sys.stdout.flush()
+    result_fd = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(obj):
+        os.write(result_fd, (json.dumps(obj) + "\n").encode())
     if args.warmup < 3:
         args.warmup = 3
 
@@ -281,7 +290,7 @@ def main():
                 "cpu_baseline": {"value": v, "unit": "Msamples/s", "cores": used, "kind": kind, "sample": desc},
                 "e2e": {"value": v, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
-        print(json.dumps(line))
+        emit(line)
         return 0
 
     import torch
@@ -423,7 +432,7 @@ def main():
                            "l2": "input %.0f MiB + rows %.0f MiB per step, larger than L2" % (4 * S / 2**20, 4 * BINS * F / 2**20)},
                 "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "clocks": clocks,
                 "gpu_launches": int(launches)}
-        print(json.dumps(line))
+        emit(line)
     if dist is not None:
         dist.destroy_process_group()
     return 0

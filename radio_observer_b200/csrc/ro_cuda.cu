@@ -125,6 +125,12 @@ struct ro_wf {
 	int stagger_small;                    // the same for the 256-thread kernels (4k, 8k; RO_STAGGER_SMALL)
 	ro::V2Kernel v2s;
 	int v2s_grid_cap;
+	// 32k and 64k frames of int16 input: radix-Na step fused into the 16k kernel (MODE_FUSED*), the
+	// only scratch is a CTA-private slice that stays in L2
+	bool fused_ok;
+	ro::V2Kernel v2f;
+	int v2f_grid_cap;
+	void *d_fscratch;
 	int log2na;
 	float2 *d_tw_nb;                      // exp(-2*pi*i*j/16384)
 	void   *d_scratch;                    // [scratch_frames][N] packed complex float
@@ -349,6 +355,25 @@ int launch_fft(ro_wf *h, cudaStream_t s, const void *d_iq, float *d_rows, long l
 		}
 		return RO_OK;
 	}
+	if (h->fused_ok && ((uintptr_t)d_rows & 15) == 0 && (row_stride & 3) == 0) {
+		const long long cap = h->v2f_grid_cap;
+		const long long fpc = (n_frames + cap - 1) / cap;          // contiguous frames per CTA
+		const int grid = (int)((n_frames + fpc - 1) / fpc);
+		cudaEvent_t e0 = 0, e1 = 0;
+		if (h->profiling) {
+			int rc = get_event(h, &e0); if (rc) return rc;
+			rc = get_event(h, &e1); if (rc) return rc;
+			CU(cudaEventRecord(e0, s));
+		}
+		CU(ro::v2_launch_fused(h->v2f, grid, s, d_iq, h->d_window, h->d_tw, h->d_tw_nb, h->d_fscratch, d_rows,
+		                       row_stride, n_frames, h->hop, fpc, (float)h->cfg.iq_gain, 1, h->stagger));
+		h->launches++;
+		if (h->profiling) {
+			CU(cudaEventRecord(e1, s));
+			h->ev_used[0].push_back(std::make_pair(e0, e1));
+		}
+		return RO_OK;
+	}
 	if (h->split_ok) {
 		cudaEvent_t e0 = 0, e1 = 0;
 		if (h->profiling) {
@@ -509,6 +534,7 @@ void free_all(ro_wf *h)
 	cudaFree(h->d_tw_nb);
 	cudaFree(h->d_scratch);
 	cudaFree(h->d_rscratch);
+	cudaFree(h->d_fscratch);
 	cudaFree(h->d_tw64);
 	cudaFree(h->d_x64);
 	if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -687,6 +713,20 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 			h->scratch_frames = units * unit;
 			CUH(cudaMalloc(&h->d_scratch, (size_t)(h->scratch_frames * frame_bytes)));
 			h->split_ok = true;
+		}
+	}
+	h->fused_ok = false;
+	if (h->split_ok && log2nb == 14 && (h->log2na == 1 || h->log2na == 2) && h->fmt == ro::FMT_INT16 &&
+	    !getenv("RO_NO_FUSED") &&
+	    ro::v2_pick(14, h->log2na == 1 ? ro::V2_FUSED1 : ro::V2_FUSED2, false, &h->v2f)) {
+		CUH(cudaFuncSetAttribute(h->v2f.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->v2f.smem));
+		int occ4 = 0;
+		CUH(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, h->v2f.fn, h->v2f.threads, h->v2f.smem));
+		if (occ4 >= 1) {
+			h->v2f_grid_cap = occ4 * h->n_sms;
+			const size_t per_cta = (((size_t)1 << h->log2na) - 1) * ((size_t)1 << 14) * sizeof(float2);
+			CUH(cudaMalloc(&h->d_fscratch, per_cta * (size_t)h->v2f_grid_cap));
+			h->fused_ok = true;
 		}
 	}
 	CUH(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));

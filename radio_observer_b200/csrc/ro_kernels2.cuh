@@ -40,13 +40,20 @@ struct Wf2Params {
 	int           stagger;      // serialise the shared-memory load bursts of the warps that share a scheduler
 	int           pair;         // MODE_SPLIT: rows are 16-byte aligned and every CTA starts on an even item:
 	                            // classes r, r+1 are stored together (see the store stage)
+	// MODE_FUSED*: the first radix-Na step happens in this kernel (see the load stage)
+	const void   *raw;          // int16 I/Q of the whole batch
+	const float  *window_full;  // Na*N floats
+	const float2 *tw_big;       // Na*N entries exp(-2*pi*i*j/(Na*N))
+	unsigned long long *scratch;// [gridDim.x][Na-1][N] packed complex, private to each CTA (stays in L2)
 };
 
 // where the N points of one item come from / where its magnitudes go
 enum { MODE_DIRECT = 0,   // int16 I/Q read from global memory, row = item
        MODE_STAGED = 1,   // int16 I/Q through the TMA-staged shared-memory ring, row = item
-       MODE_SPLIT  = 2 }; // packed complex float from wf_split_kernel (already windowed, first
+       MODE_SPLIT  = 2,   // packed complex float from wf_split_kernel (already windowed, first
                           // radix-Na step done): item = frame*Na + r, output k is bin Na*k + r
+       MODE_FUSED1 = 3,   // like MODE_SPLIT with Na = 2, 4, but the radix-Na step is done here, per frame,
+       MODE_FUSED2 = 4 }; // by the thread that needs its results: no scratch round trip through HBM
 
 __device__ __forceinline__ unsigned int smem_u32(const void *p)
 {
@@ -126,8 +133,8 @@ constexpr size_t wf2_smem_bytes()
 {
 	constexpr size_t N = (size_t)1 << LOG2N;
 	constexpr size_t PAD1 = (R3 < 16) ? R3 : 0;
-	return sizeof(c64) * (N + P * PAD1) + (MODE == MODE_SPLIT ? 0 : sizeof(float) * (N / 2)) + 32 +
-	       (MODE == MODE_STAGED ? 4 * N : 0) + (MODE == MODE_SPLIT && P / R3 >= 2 ? 4 * N : 0);
+	return sizeof(c64) * (N + P * PAD1) + (MODE >= MODE_SPLIT ? 0 : sizeof(float) * (N / 2)) + 32 +
+	       (MODE == MODE_STAGED ? 4 * N : 0) + (MODE >= MODE_SPLIT && P / R3 >= 2 ? 4 * N : 0);
 }
 
 template <int LOG2N, int P, int R3, int MODE, bool GAIN, int MINB>
@@ -135,7 +142,9 @@ __global__ void __launch_bounds__((1 << LOG2N) / P, MINB)
 wf_fft2_kernel(const Wf2Params p)
 {
 	constexpr bool STAGE = MODE == MODE_STAGED;
-	constexpr bool SPLIT = MODE == MODE_SPLIT;
+	constexpr bool FUSED = MODE >= MODE_FUSED1;
+	constexpr int FLA = FUSED ? MODE - MODE_FUSED1 + 1 : 0;   // log2(Na) of the fused modes
+	constexpr bool SPLIT = MODE == MODE_SPLIT || FUSED;
 	constexpr int WINF = SPLIT ? 0 : (1 << LOG2N) / 2;      // floats of window table in shared memory
 	constexpr int N = 1 << LOG2N;
 	constexpr int R1 = P, R2 = P;
@@ -231,6 +240,49 @@ wf_fft2_kernel(const Wf2Params p)
 			for (int n1 = 0; n1 < R1; n1++) {
 				const c64 x = short2_to_c64(raw[n1]);
 				v[n1] = mul2(GAIN ? add2(x, gain2) : x, pk(wv[n1], wv[n1]));
+			}
+		} else if (FUSED) {
+			// Frame F = f >> FLA of Na*N points, residue class r = f & (Na-1):
+			//     y_r[m] = W_{Na*N}^{m*r} * sum_q xw[q*N + m] * W_Na^{q*r},   X[Na*k + r] = DFT_N(y_r)[k]
+			// Pass 1 of every class needs y_r at m = n1*M + t, n1 = 0..R1-1: the SAME m for every r.  So at
+			// r = 0 this thread loads its Na*R1 samples once, does R1 Na-point transforms, keeps y_0 as its
+			// pass-1 input and parks y_1 .. y_{Na-1} in a slice of global memory that only this CTA touches
+			// (Na-1 x 128 KB, rewritten every frame: it lives in L2); at r > 0 it reads back what it wrote
+			// itself, so no barrier is involved.  wf_split_kernel + MODE_SPLIT did the same arithmetic with a
+			// frame-sized scratch for the whole batch, i.e. a round trip of 16 B per point through HBM.
+			if constexpr (FUSED) {
+			constexpr int NA = 1 << FLA;
+			constexpr int NBIG = N << FLA;
+			const int r = (int)(f & (NA - 1));
+			unsigned long long *scr = p.scratch + (size_t)blockIdx.x * (NA - 1) * N;
+			if (r == 0) {
+				const unsigned int *src = reinterpret_cast<const unsigned int *>(p.raw) + (f >> FLA) * hop;
+				const unsigned long long *twb = reinterpret_cast<const unsigned long long *>(p.tw_big);
+#pragma unroll
+				for (int n1 = 0; n1 < R1; n1++) {
+					const int m = n1 * M + t;
+					c64 xq[NA];
+#pragma unroll
+					for (int q = 0; q < NA; q++) {
+						const float w = __ldg(p.window_full + q * N + m);
+						xq[q] = mul2(add2(short2_to_c64(__ldg(src + q * N + m)), gain2), pk(w, w));
+					}
+					fft_dif2<NA>(xq);
+					c64 bb[FLA];
+#pragma unroll
+					for (int i = 0; i < FLA; i++) bb[i] = __ldg(twb + ((m << i) & (NBIG - 1)));
+					twiddle_powers2<NA>(xq, bb);
+					v[n1] = xq[0];
+#pragma unroll
+					for (int rr = 1; rr < NA; rr++) scr[(rr - 1) * N + m] = xq[bitrev(rr, FLA)];
+				}
+			} else {
+				const unsigned long long *src = scr + (r - 1) * N;
+				ptxas_fence(p.stagger & 1);
+#pragma unroll
+				for (int n1 = 0; n1 < R1; n1++) v[n1] = __ldcg(src + n1 * M + t);
+				ptxas_fence(p.stagger & 1);
+			}
 			}
 		} else if (SPLIT) {
 			const unsigned long long *src = reinterpret_cast<const unsigned long long *>(p.iq) + f * N;

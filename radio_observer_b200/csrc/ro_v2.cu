@@ -31,6 +31,21 @@ bool pick_one(int mode, bool gain, V2Kernel *k)
 
 bool v2_pick(int log2n, int mode, bool gain, V2Kernel *out)
 {
+	if (mode == V2_FUSED1 || mode == V2_FUSED2) {
+		if (log2n != 14) return false;
+		out->log2n = log2n;
+		out->mode = mode;
+		out->gain = false;                       // the gain is a kernel parameter here
+		out->threads = (1 << 14) / 32;
+		if (mode == V2_FUSED1) {
+			out->smem = wf2_smem_bytes<14, 32, 16, MODE_FUSED1>();
+			out->fn = (const void *)wf_fft2_kernel<14, 32, 16, MODE_FUSED1, false, 1>;
+		} else {
+			out->smem = wf2_smem_bytes<14, 32, 16, MODE_FUSED2>();
+			out->fn = (const void *)wf_fft2_kernel<14, 32, 16, MODE_FUSED2, false, 1>;
+		}
+		return true;
+	}
 	if (mode == V2_SPLIT) {
 		out->log2n = log2n;
 		out->mode = mode;
@@ -86,6 +101,37 @@ cudaError_t v2_launch(const V2Kernel &k, int grid, cudaStream_t s, const void *d
 	p.log2na = log2na;
 	p.pair = pair;
 	p.stagger = stagger;
+	p.raw = NULL;
+	p.window_full = NULL;
+	p.tw_big = NULL;
+	p.scratch = NULL;
+	void *args[] = { &p };
+	return cudaLaunchKernel(k.fn, dim3(grid), dim3(k.threads), args, k.smem, s);
+}
+
+cudaError_t v2_launch_fused(const V2Kernel &k, int grid, cudaStream_t s, const void *d_raw, const float *d_window_full,
+                            const float2 *d_tw_big, const float2 *d_tw_nb, void *d_scratch, float *d_rows,
+                            long long row_stride, long long n_frames, long long hop, long long frames_per_cta,
+                            float iq_gain, int pair, int stagger)
+{
+	const int la = k.mode - V2_FUSED1 + 1;
+	Wf2Params p;
+	p.iq = NULL;
+	p.window_half = NULL;
+	p.tw = d_tw_nb;
+	p.rows = d_rows;
+	p.n_frames = n_frames << la;                 // items
+	p.hop = hop;
+	p.row_stride = row_stride;
+	p.frames_per_cta = frames_per_cta << la;     // a CTA owns whole frames
+	p.iq_gain = iq_gain;
+	p.log2na = la;
+	p.pair = pair;
+	p.stagger = stagger;
+	p.raw = d_raw;
+	p.window_full = d_window_full;
+	p.tw_big = d_tw_big;
+	p.scratch = reinterpret_cast<unsigned long long *>(d_scratch);
 	void *args[] = { &p };
 	return cudaLaunchKernel(k.fn, dim3(grid), dim3(k.threads), args, k.smem, s);
 }

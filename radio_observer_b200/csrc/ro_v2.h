@@ -5,7 +5,7 @@
 
 namespace ro {
 
-enum { V2_DIRECT = 0, V2_STAGED = 1, V2_SPLIT = 2 };   // = MODE_* of ro_kernels2.cuh
+enum { V2_DIRECT = 0, V2_STAGED = 1, V2_SPLIT = 2, V2_FUSED1 = 3, V2_FUSED2 = 4 };   // = MODE_* of ro_kernels2.cuh
 
 struct V2Kernel {
 	const void *fn;      // kernel symbol (for attribute / occupancy queries)
@@ -27,6 +27,13 @@ bool v2_pick(int log2n, int mode, bool gain, V2Kernel *out);
 cudaError_t v2_launch(const V2Kernel &k, int grid, cudaStream_t s, const void *d_iq, const float *d_window_half,
                       const float2 *d_tw, float *d_rows, long long row_stride, long long n_frames, long long hop,
                       long long frames_per_cta, float iq_gain, int log2na, int pair, int stagger);
+
+// V2_FUSED1 / V2_FUSED2 (frames of 2*16384 / 4*16384 points, int16 input): one launch does the radix-Na
+// step and the Na 16k transforms of each frame; d_scratch holds grid * (Na-1) * 16384 packed complex.
+cudaError_t v2_launch_fused(const V2Kernel &k, int grid, cudaStream_t s, const void *d_raw, const float *d_window_full,
+                            const float2 *d_tw_big, const float2 *d_tw_nb, void *d_scratch, float *d_rows,
+                            long long row_stride, long long n_frames, long long hop, long long frames_per_cta,
+                            float iq_gain, int pair, int stagger);
 
 // First radix-Na step of frames frame0 .. frame0+n_frames-1 (N = 2^log2n points, Na = 2^log2na)
 // into d_y[n_frames][Na][N/Na] (packed complex float).  f32in: float32 I/Q instead of int16.
