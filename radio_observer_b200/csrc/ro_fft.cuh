@@ -39,6 +39,17 @@ __host__ __device__ constexpr float sw32(int j)
 	return cw32(j <= 8 ? 8 - j : j - 8);
 }
 
+// cos(2*pi*j/64), sin(2*pi*j/64) for j = 0..32
+__host__ __device__ constexpr float cw64(int j)
+{
+	constexpr float T[17] = {1.000000000e+00f, 9.951847267e-01f, 9.807852804e-01f, 9.569403357e-01f, 9.238795325e-01f,
+	                         8.819212643e-01f, 8.314696123e-01f, 7.730104534e-01f, 7.071067812e-01f, 6.343932842e-01f,
+	                         5.555702330e-01f, 4.713967368e-01f, 3.826834324e-01f, 2.902846773e-01f, 1.950903220e-01f,
+	                         9.801714033e-02f, 0.0f};
+	return j <= 16 ? T[j] : -T[32 - j];
+}
+__host__ __device__ constexpr float sw64(int j) { return j <= 16 ? cw64(16 - j) : cw64(j - 16); }
+
 __host__ __device__ constexpr int ilog2(int v) { return v <= 1 ? 0 : 1 + ilog2(v >> 1); }
 
 __host__ __device__ constexpr int bitrev(int v, int bits)

@@ -145,6 +145,10 @@ wf_fft2_kernel(const Wf2Params p)
 	constexpr bool FUSED = MODE >= MODE_FUSED1;
 	constexpr int FLA = FUSED ? MODE - MODE_FUSED1 + 1 : 0;   // log2(Na) of the fused modes
 	constexpr bool SPLIT = MODE == MODE_SPLIT || FUSED;
+#ifndef RO_FUSED_DIT
+#define RO_FUSED_DIT 1
+#endif
+	constexpr bool USE_DIT = !SPLIT || (FUSED && RO_FUSED_DIT);
 	constexpr int WINF = SPLIT ? 0 : (1 << LOG2N) / 2;      // floats of window table in shared memory
 	constexpr int N = 1 << LOG2N;
 	constexpr int R1 = P, R2 = P;
@@ -258,23 +262,48 @@ wf_fft2_kernel(const Wf2Params p)
 			if (r == 0) {
 				const unsigned int *src = reinterpret_cast<const unsigned int *>(p.raw) + (f >> FLA) * hop;
 				const unsigned long long *twb = reinterpret_cast<const unsigned long long *>(p.tw_big);
+				// loads in bursts of CH positions m, fenced from the arithmetic and the stores: one memory
+				// latency per burst instead of one per position (ptxas will not move loads above the stores)
+				// Na = 2: the one twiddle W_{2N}^m, m = n1*M + t, is W_{2N}^t (one load per frame) times the
+				// compile-time constant W_{2N/M}^{n1} = W_64^{n1}: two more FFMA2 instead of 32 loads
+				constexpr bool TWC = NA == 2 && NBIG / M == 64;
+				c64 wt = pk(1.f, 0.f);
+				if (TWC) wt = __ldg(twb + t);
+				constexpr int CH = 16 / NA;
 #pragma unroll
-				for (int n1 = 0; n1 < R1; n1++) {
-					const int m = n1 * M + t;
-					c64 xq[NA];
+				for (int c0 = 0; c0 < R1; c0 += CH) {
+					unsigned int raw[CH][NA];
+					float wv[CH][NA];
+					c64 bb[CH][FLA];
+					ptxas_fence(p.stagger & 1);
 #pragma unroll
-					for (int q = 0; q < NA; q++) {
-						const float w = __ldg(p.window_full + q * N + m);
-						xq[q] = mul2(add2(short2_to_c64(__ldg(src + q * N + m)), gain2), pk(w, w));
+					for (int j = 0; j < CH; j++) {
+						const int m = (c0 + j) * M + t;
+#pragma unroll
+						for (int q = 0; q < NA; q++) {
+							raw[j][q] = __ldg(src + q * N + m);
+							wv[j][q] = __ldg(p.window_full + q * N + m);
+						}
+						if (!TWC) {
+#pragma unroll
+							for (int i = 0; i < FLA; i++) bb[j][i] = __ldg(twb + ((m << i) & (NBIG - 1)));
+						}
 					}
-					fft_dif2<NA>(xq);
-					c64 bb[FLA];
+					ptxas_fence(p.stagger & 1);
 #pragma unroll
-					for (int i = 0; i < FLA; i++) bb[i] = __ldg(twb + ((m << i) & (NBIG - 1)));
-					twiddle_powers2<NA>(xq, bb);
-					v[n1] = xq[0];
+					for (int j = 0; j < CH; j++) {
+						const int m = (c0 + j) * M + t;
+						c64 xq[NA];
 #pragma unroll
-					for (int rr = 1; rr < NA; rr++) scr[(rr - 1) * N + m] = xq[bitrev(rr, FLA)];
+						for (int q = 0; q < NA; q++)
+							xq[q] = mul2(add2(short2_to_c64(raw[j][q]), gain2), pk(wv[j][q], wv[j][q]));
+						fft_dif2<NA>(xq);
+						if (TWC) xq[1] = cmul2(cmul2(xq[1], wt), cw64((c0 + j) & 31), -sw64((c0 + j) & 31));
+						else twiddle_powers2<NA>(xq, bb[j]);
+						v[c0 + j] = xq[0];
+#pragma unroll
+						for (int rr = 1; rr < NA; rr++) scr[(rr - 1) * N + m] = xq[bitrev(rr, FLA)];
+					}
 				}
 			} else {
 				const unsigned long long *src = scr + (r - 1) * N;
@@ -309,7 +338,7 @@ wf_fft2_kernel(const Wf2Params p)
 		}
 
 		// ---- pass 1 ----
-		fft_fwd2<R1, !SPLIT>(v);
+		fft_fwd2<R1, USE_DIT>(v);
 		RO_SITE(0, p.stagger & 1);
 		twiddle_powers2<R1>(v, b1);
 		RO_SITE(1, p.stagger & 1);
@@ -354,7 +383,7 @@ wf_fft2_kernel(const Wf2Params p)
 			for (int n2 = 0; n2 < R2; n2++) v[n2] = S[k1 * ROW1 + n2 * R3 + n3];
 			if (CHAIN && (p.stagger & 2)) chain_pass(wq, wl, LEVELS, cdist);
 			if (!INPLACE) mbar_arrive(bar_rd2);         // my pass-2 inputs are in registers
-			fft_fwd2<R2, !SPLIT>(v);
+			fft_fwd2<R2, USE_DIT>(v);
 			RO_SITE(2, p.stagger & 1);
 			twiddle_powers2<R2>(v, b2);
 			RO_SITE(3, p.stagger & 1);
@@ -417,7 +446,7 @@ wf_fft2_kernel(const Wf2Params p)
 				c64 w[R3];
 #pragma unroll
 				for (int n3 = 0; n3 < R3; n3++) w[n3] = u[c * R3 + n3];
-				fft_fwd2<R3, !SPLIT>(w);
+				fft_fwd2<R3, USE_DIT>(w);
 #pragma unroll
 				for (int k3 = 0; k3 < R3; k3++) {
 					float zr, zi;
@@ -491,7 +520,7 @@ wf_fft2_kernel(const Wf2Params p)
 #pragma unroll
 			for (int n3 = 0; n3 < R3; n3++) u[n3] = S[((t / R1) * R3 + n3) * R1 + ((t % R1) ^ (n3 * SW))];
 			mbar_arrive(bar_rd3);
-			fft_fwd2<R3, !SPLIT>(u);
+			fft_fwd2<R3, USE_DIT>(u);
 #pragma unroll
 			for (int k3 = 0; k3 < R3; k3++) {
 				const int off = (k3 * (N / R3) + N / 2) & NMASK;   // t < N/R3 = T

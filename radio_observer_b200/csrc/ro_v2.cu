@@ -31,19 +31,15 @@ bool pick_one(int mode, bool gain, V2Kernel *k)
 
 bool v2_pick(int log2n, int mode, bool gain, V2Kernel *out)
 {
-	if (mode == V2_FUSED1 || mode == V2_FUSED2) {
+	if (mode == V2_FUSED2) return false;         // measured slower than the split path at 64k: not instantiated
+	if (mode == V2_FUSED1) {
 		if (log2n != 14) return false;
 		out->log2n = log2n;
 		out->mode = mode;
 		out->gain = false;                       // the gain is a kernel parameter here
 		out->threads = (1 << 14) / 32;
-		if (mode == V2_FUSED1) {
-			out->smem = wf2_smem_bytes<14, 32, 16, MODE_FUSED1>();
-			out->fn = (const void *)wf_fft2_kernel<14, 32, 16, MODE_FUSED1, false, 1>;
-		} else {
-			out->smem = wf2_smem_bytes<14, 32, 16, MODE_FUSED2>();
-			out->fn = (const void *)wf_fft2_kernel<14, 32, 16, MODE_FUSED2, false, 1>;
-		}
+		out->smem = wf2_smem_bytes<14, 32, 16, MODE_FUSED1>();
+		out->fn = (const void *)wf_fft2_kernel<14, 32, 16, MODE_FUSED1, false, 1>;
 		return true;
 	}
 	if (mode == V2_SPLIT) {
