@@ -162,8 +162,19 @@ class ClockSampler:
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "ref_oracle")
 
 
-def ref_config_json(out_dir):
-    return json.dumps({
+CUDA_BIN = os.path.join(ROOT, "radio_observer_b200", "host", "_build", "radio-observer-cuda")
+
+
+def ref_config_json(out_dir, factory="waterfall", extra=None):
+    cfg = _ref_config(out_dir)
+    be = cfg["configurations"][0]["children"][0]
+    be["factory"] = factory
+    be.update(extra or {})
+    return json.dumps(cfg, indent=1)
+
+
+def _ref_config(out_dir):
+    return ({
         "configuration": "default",
         "configurations": [{
             "key": "default", "factory": "pipeline",
@@ -179,7 +190,7 @@ def ref_config_json(out_dir):
                      "low_freq": SNAP_BAND_HZ[0], "hi_freq": SNAP_BAND_HZ[1],
                      "low_detect_freq": DETECT_HZ[0], "hi_detect_freq": DETECT_HZ[1],
                      "low_noise_freq": NOISE_HZ[0], "hi_noise_freq": NOISE_HZ[1], "avg_freq_range": AVG_HZ},
-                ]}]}]}, indent=1)
+                ]}]}]})
 
 
 def host_station_iq(n_samples, seed):
@@ -189,23 +200,26 @@ def host_station_iq(n_samples, seed):
     return synth.generate_int16(spec)
 
 
-def run_reference_cpu(sample_seconds, procs):
+def run_reference_cpu(sample_seconds, procs, binary=None, factory="waterfall", extra=None, wav_path=None):
     """Time the reference's own C++ classes (or, if the binary is absent, the numpy port)
     on `procs` independent time shards of sample_seconds each.  Returns
-    (Msamples/s, kind, cores, description)."""
+    (Msamples/s, kind, cores, description).  With binary=CUDA_BIN, factory="waterfall_cuda" the
+    same Pipeline runs with the CUDA backend behind the adapter (the drop-in measurement)."""
+    binary = binary or REF_BIN
     from radio_observer_b200 import synth
     n = int(sample_seconds * SR)
     n -= n % 1024
     base = "/dev/shm" if os.path.isdir("/dev/shm") else None
     tmp = tempfile.mkdtemp(prefix="ro_bench_", dir=base)
     try:
-        if os.path.exists(REF_BIN):
-            wav = os.path.join(tmp, "in.wav")
-            synth.write_wav(wav, host_station_iq(n, 0x5EED0002), SR)
+        if os.path.exists(binary):
+            wav = wav_path or os.path.join(tmp, "in.wav")
+            if not wav_path:
+                synth.write_wav(wav, host_station_iq(n, 0x5EED0002), SR)
             for p in range(procs):
                 d = os.path.join(tmp, "p%d" % p)
                 os.makedirs(os.path.join(d, "out"))
-                open(os.path.join(d, "cfg.json"), "w").write(ref_config_json(os.path.join(d, "out")))
+                open(os.path.join(d, "cfg.json"), "w").write(ref_config_json(os.path.join(d, "out"), factory, extra))
             times = [None] * procs
 
             def worker(p):
@@ -214,7 +228,7 @@ def run_reference_cpu(sample_seconds, procs):
                 # constructor) and sometimes aborts before processing: retry
                 for attempt in range(25):
                     t0 = time.perf_counter()
-                    rc = subprocess.call([REF_BIN, "-c", os.path.join(d, "cfg.json"), "-q", wav],
+                    rc = subprocess.call([binary, "-c", os.path.join(d, "cfg.json"), "-q", wav],
                                          stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, cwd=d)
                     if rc == 0:
                         times[p] = time.perf_counter() - t0
@@ -230,6 +244,8 @@ def run_reference_cpu(sample_seconds, procs):
                         "%d concurrent process(es), each %.0f s of 96 kHz station I/Q (WAV in tmpfs) through the "
                         "reference's own Pipeline/WAVStream/WaterfallBackend/BolidRecorder (oracle/_ref, -O2, shim "
                         "FFT because FFTW is absent), FITS to tmpfs" % (procs, n / SR))
+        if binary != REF_BIN:
+            return None
         # port: numpy restatement, single thread
         from oracle import ref_numpy as R
         iq = host_station_iq(n, 0x5EED0002)
@@ -417,9 +433,35 @@ def main():
            "output": "recorder band rows (%d bins) + detector records" % wf.row_width, "checksum": checksum}
 
     cpu_baseline = None
+    dropin = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        v, kind, cores, desc = run_reference_cpu(300.0, 1)
-        cpu_baseline = {"value": v, "unit": "Msamples/s", "cores": cores, "kind": kind, "sample": desc}
+        # 30 min of station data: about 11 s of work for the reference on one core
+        secs = 1800.0
+        from radio_observer_b200 import synth
+        base = "/dev/shm" if os.path.isdir("/dev/shm") else None
+        wtmp = tempfile.mkdtemp(prefix="ro_bench_wav_", dir=base)
+        try:
+            wav = None
+            if os.path.exists(REF_BIN):
+                n = int(secs * SR)
+                n -= n % 1024
+                wav = os.path.join(wtmp, "in.wav")
+                synth.write_wav(wav, host_station_iq(n, 0x5EED0002), SR)
+            v, kind, cores, desc = run_reference_cpu(secs, 1, wav_path=wav)
+            cpu_baseline = {"value": v, "unit": "Msamples/s", "cores": cores, "kind": kind, "sample": desc}
+            # the same WAV through the reference's own Pipeline with one string changed in the config
+            # ("factory": "waterfall_cuda"): what a station operator gets today.  The reference's host side
+            # (WAVStream -> vector<Complex>, one raw-ring push per sample, recorders, FITS) is unchanged and
+            # bounds this number; process start-up and CUDA initialisation (about 1.3 s) are inside it.
+            wf.close()
+            r = run_reference_cpu(secs, 1, binary=CUDA_BIN, factory="waterfall_cuda",
+                                  extra={"cuda_batch_frames": 64}, wav_path=wav) if wav else None
+            if r is not None:
+                dropin = {"value": r[0], "unit": "Msamples/s", "cores": 1,
+                          "what": "reference Pipeline/WAVStream/recorders unmodified, backend factory waterfall_cuda "
+                                  "(cuda_batch_frames 64), same %.0f s WAV and outputs as cpu_baseline" % secs}
+        finally:
+            shutil.rmtree(wtmp, ignore_errors=True)
 
     if rank == 0:
         line = {"metric": "complex Msamples/s through waterfall FFT+magnitude+bolid detect",
@@ -430,7 +472,7 @@ def main():
                            "samples_per_gpu_per_step": S, "frames_per_gpu_per_step": F,
                            "sharding": "time shards, one per GPU, overlap halo re-read from input; no collective",
                            "l2": "input %.0f MiB + rows %.0f MiB per step, larger than L2" % (4 * S / 2**20, 4 * BINS * F / 2**20)},
-                "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "clocks": clocks,
+                "roofline": roofline, "cpu_baseline": cpu_baseline, "dropin": dropin, "e2e": e2e, "clocks": clocks,
                 "gpu_launches": int(launches)}
         emit(line)
     if dist is not None:

@@ -61,14 +61,14 @@ void CudaWaterfallBackend::startStream(StreamInfo info)
 	fill_ = 0;
 	info_ = DataInfo();
 	pending_.clear();
-	windowRaw_.assign(bins_, RawDataHandle());
+	toNextHop_ = 0;
+	hopHandles_.clear();
 	{
 		int cap = (1 << 22) / bins_;          // about 16 MiB of harvested rows at a time
 		if (cap < 1) cap = 1;
 		if (cap > 64) cap = 64;
 		rows_.resize((size_t)bins_ * cap);
 	}
-	asComplex_.assign(2 * (size_t)bins_, 0.0);
 	delivered_ = 0;
 	failed_ = false;
 
@@ -94,12 +94,18 @@ void CudaWaterfallBackend::startStream(StreamInfo info)
 
 void CudaWaterfallBackend::pushSamples(const Complex *src, int count, WFTime timeOffset)
 {
+	// raw I/Q ring: one push per sample like src/FFTBackend.cpp:218; the handle (ring mark after the
+	// push, stream time of the sample) only where a frame can start
 	for (int i = 0; i < count; i++) {
 		floatToInt(src[i], rawBuffer_.push());
-		windowRaw_[fill_ + i] = RawDataHandle(
-			rawBuffer_.mark(),
-			timeOffset.addSamples(i, streamInfo_.sampleRate)
-		);
+		if (toNextHop_ == 0) {
+			hopHandles_.push_back(RawDataHandle(
+				rawBuffer_.mark(),
+				timeOffset.addSamples(i, streamInfo_.sampleRate)
+			));
+			toNextHop_ = bins_ - overlap_;
+		}
+		toNextHop_--;
 	}
 	if (ro_wf_push(wf_, src, (size_t)count) != RO_OK) fail("ro_wf_push");
 }
@@ -118,23 +124,26 @@ void CudaWaterfallBackend::process(const std::vector<Complex> &data, DataInfo in
 		pushSamples(src, count, timeOffset);
 		if (failed_) return;
 
-		info_.timeOffset = windowRaw_[0].time;
+		// windowRaw_[0] of the full window, then of the shifted one (src/FFTBackend.cpp:241-251):
+		// with overlap 0 nothing is shifted and both are the same handle
+		info_.timeOffset = hopHandles_[0].time;
+		PendingFrame p;
+		p.info = info_;
+		p.rawMark = overlap_ > 0 ? hopHandles_[1].mark : hopHandles_[0].mark;
+		pending_.push_back(p);
+		hopHandles_.pop_front();
 
-		const int hop = bins_ - overlap_;
-		memmove(&windowRaw_[0], &windowRaw_[0] + hop, overlap_ * sizeof(windowRaw_[0]));
 		fill_ = overlap_;
 		size -= count;
 		src += count;
 
-		PendingFrame p;
-		p.info = info_;
-		p.rawMark = windowRaw_[0].mark;
-		pending_.push_back(p);
-
 		timeOffset = timeOffset.addSamples(count, streamInfo_.sampleRate);
 		info_.offset++;
 
-		if ((int)pending_.size() >= batchFrames_) harvest(true);
+		// realtime (batch 1): the row is with the recorders before process() returns.  Otherwise rows
+		// are taken over one batch late, while the GPU works on the next one.
+		if (batchFrames_ <= 1) harvest(true);
+		else if ((int)pending_.size() >= 2 * batchFrames_) harvest(false, batchFrames_);
 		if (failed_) return;
 	}
 
@@ -145,26 +154,30 @@ void CudaWaterfallBackend::process(const std::vector<Complex> &data, DataInfo in
 }
 
 
-void CudaWaterfallBackend::harvest(bool flush)
+void CudaWaterfallBackend::harvest(bool flush, int atMost)
 {
 	if (flush && ro_wf_flush(wf_) != RO_OK) { fail("ro_wf_flush"); return; }
-	const int half = bins_ / 2;
 	const size_t cap = rows_.size() / (size_t)bins_;
-	while (!pending_.empty()) {
+	size_t want = atMost > 0 ? (size_t)atMost : pending_.size();
+	while (want > 0 && !pending_.empty()) {
 		size_t n = 0;
 		uint64_t first = 0;
-		if (ro_wf_poll(wf_, &rows_[0], cap, NULL, &n, &first) != RO_OK) { fail("ro_wf_poll"); return; }
+		if (ro_wf_poll(wf_, &rows_[0], cap < want ? cap : want, NULL, &n, &first) != RO_OK) { fail("ro_wf_poll"); return; }
 		if (n == 0) break;
 		for (size_t r = 0; r < n && !pending_.empty(); r++) {
-			const float *row = &rows_[r * (size_t)bins_];
-			// undo the fftshift: processFFT writes data[i] to row[(i + half) % bins_]
-			for (int i = 0; i < half; i++) asComplex_[2 * i] = row[half + i];
-			for (int i = half; i < bins_; i++) asComplex_[2 * i] = row[i - half];
+			// what processFFT does after its magnitude loop (src/WaterfallBackend.cpp:488,507,534-536):
+			// the GPU row is already magnitude, fftshifted, float
+			float *row = buffer_.push();
+			memcpy(row, &rows_[r * (size_t)bins_], sizeof(float) * (size_t)bins_);
 			PendingFrame p = pending_.front();
 			pending_.pop_front();
-			WaterfallBackend::processFFT((const fftw_complex *)&asComplex_[0], bins_, p.info, p.rawMark);
+			rawHandles_[buffer_.mark()] = RawDataHandle(p.rawMark, p.info.timeOffset);
+			FOR_EACH(recorders_, it) {
+				(*it)->update();
+			}
 			delivered_++;
 		}
+		want -= n < want ? n : want;
 	}
 }
 

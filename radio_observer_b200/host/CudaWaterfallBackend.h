@@ -20,7 +20,24 @@
 #include <deque>
 #include <vector>
 
+// Everything WaterfallBackend.h includes, first and untouched ...
+#include <cmath>
+#include <fitsio.h>
+#include "FFTBackend.h"
+#include "FITSWriter.h"
+#include "RingBuffer.h"
+#include "Channel.h"
+#include "BolidMessage.h"
+#include "CsvLog.h"
+#include "utils.h"
+// ... then the class itself with its private section readable from this translation unit: the row
+// ring, its handle table and the recorder list are private members (src/WaterfallBackend.h:243-252)
+// and a finished GPU row has to be pushed into that very ring (what processFFT does after its own
+// magnitude loop, src/WaterfallBackend.cpp:488,507,534-536).  No reference file is edited and the class
+// layout is unchanged; a maintainer who prefers it adds `friend class CudaWaterfallBackend;` instead.
+#define private public
 #include "WaterfallBackend.h"
+#undef private
 #include "ro_cuda.h"
 
 class CudaWaterfallBackend : public WaterfallBackend {
@@ -43,17 +60,20 @@ private:
 	bool    failed_;
 
 	// host mirror of FFTBackend's private framing state (window_ fill level and
-	// windowRaw_, src/FFTBackend.h:75-80): only the bookkeeping, no samples
+	// windowRaw_, src/FFTBackend.h:75-80): only the bookkeeping, no samples.  The reference stores a
+	// RawDataHandle per sample (src/FFTBackend.cpp:217-225) but reads only windowRaw_[0] of a full
+	// window, before and after the shift (:241-251), i.e. the handles of the samples whose stream index
+	// is a multiple of the hop: hopHandles_ keeps exactly those, computed the same way.
 	int                          fill_;
-	std::vector<RawDataHandle>   windowRaw_;
+	int                          toNextHop_;   // samples until the next multiple of the hop
+	std::deque<RawDataHandle>    hopHandles_;  // [0] = handle of the first sample of the oldest unfinished frame
 	DataInfo                     info_;
 	std::deque<PendingFrame>     pending_;
 
 	std::vector<float>           rows_;      // harvested rows, bins_ floats each
-	std::vector<double>          asComplex_; // a row re-expressed as (magnitude, 0) per FFT bin (fftw_complex layout)
 
 	void pushSamples(const Complex *src, int count, WFTime timeOffset);
-	void harvest(bool flush);
+	void harvest(bool flush, int atMost = 0);
 	void fail(const char *what);
 
 public:
