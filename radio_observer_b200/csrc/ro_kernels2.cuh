@@ -269,7 +269,10 @@ wf_fft2_kernel(const Wf2Params p)
 				constexpr bool TWC = NA == 2 && NBIG / M == 64;
 				c64 wt = pk(1.f, 0.f);
 				if (TWC) wt = __ldg(twb + t);
-				constexpr int CH = 16 / NA;
+#ifndef RO_FUSED_CH
+#define RO_FUSED_CH 16
+#endif
+				constexpr int CH = RO_FUSED_CH / NA;
 #pragma unroll
 				for (int c0 = 0; c0 < R1; c0 += CH) {
 					unsigned int raw[CH][NA];
