@@ -116,6 +116,7 @@ struct ro_wf {
 	det_kernel_t det_fn;
 	// v2 kernels (int16 input, N = 4096..16384, symmetric window): [0] direct loads, [1] TMA-staged ring
 	bool v2_ok;
+	bool v2_f32;                          // ... or, for float32 input, MODE_DIRECT_F32 in both slots
 	ro::V2Kernel v2[2];
 	int v2_grid_cap[2];
 	// frames longer than 16384 points: wf_split_kernel (first radix-Na step, once per frame) into a
@@ -402,7 +403,7 @@ int launch_fft(ro_wf *h, cudaStream_t s, const void *d_iq, float *d_rows, long l
 		return RO_OK;
 	}
 	// v2 stores 2 or 4 adjacent magnitudes with one vector store: rows must be 16-byte aligned
-	if (h->v2_ok && ((uintptr_t)d_rows & 15) == 0 && (row_stride & 3) == 0) {
+	if (h->v2_ok && ((uintptr_t)d_rows & 15) == 0 && (row_stride & 3) == 0 && (!h->v2_f32 || ((uintptr_t)d_iq & 7) == 0)) {
 		// the staged variant needs 16-byte aligned frame starts for cp.async.bulk
 		const int st = (h->hop % 4 == 0 && ((uintptr_t)d_iq & 15) == 0) ? 1 : 0;
 		const long long cap = h->v2_grid_cap[st];
@@ -654,6 +655,20 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 				CUH(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, h->v2[st].fn, h->v2[st].threads, h->v2[st].smem));
 				if (occ2 < 1) { h->v2_ok = false; break; }
 				h->v2_grid_cap[st] = occ2 * h->n_sms;
+			}
+		}
+		// float32 input (raw TCP / JACK / the adapter's narrowed Complex): the same kernel reading packed
+		// float pairs from global memory; both slots hold it, the launcher's alignment test picks either
+		h->v2_f32 = false;
+		if (sym && h->fmt == ro::FMT_FLOAT32 && !(force_v1 && force_v1[0] == '1') && !getenv("RO_NO_V2_F32") &&
+		    ro::v2_pick_f32(h->log2n, gain, &h->v2[0])) {
+			h->v2[1] = h->v2[0];
+			CUH(cudaFuncSetAttribute(h->v2[0].fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->v2[0].smem));
+			int occ2 = 0;
+			CUH(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, h->v2[0].fn, h->v2[0].threads, h->v2[0].smem));
+			if (occ2 >= 1) {
+				h->v2_grid_cap[0] = h->v2_grid_cap[1] = occ2 * h->n_sms;
+				h->v2_ok = h->v2_f32 = true;
 			}
 		}
 	}

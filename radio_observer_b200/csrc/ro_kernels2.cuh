@@ -53,7 +53,9 @@ enum { MODE_DIRECT = 0,   // int16 I/Q read from global memory, row = item
        MODE_SPLIT  = 2,   // packed complex float from wf_split_kernel (already windowed, first
                           // radix-Na step done): item = frame*Na + r, output k is bin Na*k + r
        MODE_FUSED1 = 3,   // like MODE_SPLIT with Na = 2, 4, but the radix-Na step is done here, per frame,
-       MODE_FUSED2 = 4 }; // by the thread that needs its results: no scratch round trip through HBM
+       MODE_FUSED2 = 4,   // by the thread that needs its results: no scratch round trip through HBM
+       MODE_DIRECT_F32 = 5 }; // MODE_DIRECT for float32 I/Q (the reference's raw-TCP / JACK encoding)
+constexpr bool mode_is_split(int m) { return m == MODE_SPLIT || m == MODE_FUSED1 || m == MODE_FUSED2; }
 
 __device__ __forceinline__ unsigned int smem_u32(const void *p)
 {
@@ -133,8 +135,8 @@ constexpr size_t wf2_smem_bytes()
 {
 	constexpr size_t N = (size_t)1 << LOG2N;
 	constexpr size_t PAD1 = (R3 < 16) ? R3 : 0;
-	return sizeof(c64) * (N + P * PAD1) + (MODE >= MODE_SPLIT ? 0 : sizeof(float) * (N / 2)) + 32 +
-	       (MODE == MODE_STAGED ? 4 * N : 0) + (MODE >= MODE_SPLIT && P / R3 >= 2 ? 4 * N : 0);
+	return sizeof(c64) * (N + P * PAD1) + (mode_is_split(MODE) ? 0 : sizeof(float) * (N / 2)) + 32 +
+	       (MODE == MODE_STAGED ? 4 * N : 0) + (mode_is_split(MODE) && P / R3 >= 2 ? 4 * N : 0);
 }
 
 template <int LOG2N, int P, int R3, int MODE, bool GAIN, int MINB>
@@ -142,7 +144,8 @@ __global__ void __launch_bounds__((1 << LOG2N) / P, MINB)
 wf_fft2_kernel(const Wf2Params p)
 {
 	constexpr bool STAGE = MODE == MODE_STAGED;
-	constexpr bool FUSED = MODE >= MODE_FUSED1;
+	constexpr bool FUSED = MODE == MODE_FUSED1 || MODE == MODE_FUSED2;
+	constexpr bool F32 = MODE == MODE_DIRECT_F32;
 	constexpr int FLA = FUSED ? MODE - MODE_FUSED1 + 1 : 0;   // log2(Na) of the fused modes
 	constexpr bool SPLIT = MODE == MODE_SPLIT || FUSED;
 #ifndef RO_FUSED_DIT
@@ -322,6 +325,19 @@ wf_fft2_kernel(const Wf2Params p)
 #pragma unroll
 			for (int n1 = 0; n1 < R1; n1++) v[n1] = __ldg(src + n1 * M + t);
 			ptxas_fence(p.stagger & 1);
+		} else if (F32) {
+			// float32 pairs are packed complex already: straight into the transform's registers
+			const unsigned long long *src = reinterpret_cast<const unsigned long long *>(p.iq) + f * hop;
+			float wv[R1];
+			ptxas_fence(p.stagger & 1);
+#pragma unroll
+			for (int n1 = 0; n1 < R1; n1++) {
+				v[n1] = __ldg(src + n1 * M + t);
+				wv[n1] = (n1 < R1 / 2) ? win[n1 * M + t] : win[(R1 - 1 - n1) * M + (M - 1 - t)];
+			}
+			ptxas_fence(p.stagger & 1);
+#pragma unroll
+			for (int n1 = 0; n1 < R1; n1++) v[n1] = mul2(GAIN ? add2(v[n1], gain2) : v[n1], pk(wv[n1], wv[n1]));
 		} else {
 			const unsigned int *src = reinterpret_cast<const unsigned int *>(p.iq) + f * hop;
 			unsigned int raw[R1];

@@ -5,7 +5,7 @@
 
 namespace ro {
 
-enum { V2_DIRECT = 0, V2_STAGED = 1, V2_SPLIT = 2, V2_FUSED1 = 3, V2_FUSED2 = 4 };   // = MODE_* of ro_kernels2.cuh
+enum { V2_DIRECT = 0, V2_STAGED = 1, V2_SPLIT = 2, V2_FUSED1 = 3, V2_FUSED2 = 4, V2_DIRECT_F32 = 5 };   // = MODE_* of ro_kernels2.cuh
 
 struct V2Kernel {
 	const void *fn;      // kernel symbol (for attribute / occupancy queries)
@@ -19,6 +19,9 @@ struct V2Kernel {
 // Picks the instantiation for N = 2^log2n; returns false when v2 has none.
 // mode V2_SPLIT exists for log2n = 14 only (the in-CTA part of longer frames).
 bool v2_pick(int log2n, int mode, bool gain, V2Kernel *out);
+
+// The same for float32 I/Q input (N = 1024 .. 16384), launched with v2_launch like V2_DIRECT (ro_v2f.cu).
+bool v2_pick_f32(int log2n, bool gain, V2Kernel *out);
 
 // Launches it: n_frames items of `hop`-spaced N-sample windows of d_iq (int16 I/Q), or, for
 // V2_SPLIT, n_frames = frames*Na items of N packed complex floats each (d_iq = the scratch
