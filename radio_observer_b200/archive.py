@@ -226,3 +226,45 @@ def reprocess_archive(iq: np.ndarray, bins: int, overlap: int, *, sample_rate: i
     all_rows = np.concatenate([p[0] for p in have]) if have else None
     all_det = np.concatenate([p[1] for p in have]) if have and have[0][1] is not None else None
     return all_rows, all_det, shards
+
+
+# ---------------------------------------------------------------------------
+# 8f N4  event text formats (reference src/BolidRecorder.cpp:215-257, src/CsvLog.cpp:12-58)
+# ---------------------------------------------------------------------------
+def _g(x) -> str:
+    """operator<< of a float / double on a default ostream: %g with 6 significant digits."""
+    return "%g" % float(x)
+
+
+def fft_samples_to_raw(count: int, fft_sample_rate_: np.float32, sample_rate: int) -> int:
+    """Recorder::fftSamplesToRaw with getFFTSampleRate() truncated to int
+    (reference src/WaterfallBackend.cpp:29-32, src/WaterfallBackend.h:84-87)."""
+    rate = int(fft_sample_rate_)
+    if rate == 0:
+        return 0            # the reference divides by zero here
+    return int((float(count) / float(rate)) * float(sample_rate))
+
+
+def event_fields(ev: "BolidEvent", *, sample_rate: int, bins: int, overlap: int,
+                 low_detect_freq: float, hi_detect_freq: float) -> dict:
+    """What BolidRecorder reports for an event: peak frequency, the +-quarter-band frequency window
+    (float arithmetic), duration in seconds and the raw-sample length of the snapshot."""
+    lo, hi = sorted((f32(low_detect_freq), f32(hi_detect_freq)))
+    pf = bin_to_frequency(ev.peak_bin, sample_rate, bins)
+    q = f32(f32(hi - lo) / f32(4))
+    fsr = fft_sample_rate(sample_rate, bins, clamp_overlap(bins, overlap))
+    return dict(noise=f32(ev.noise), peak_freq=pf, magnitude=f32(ev.magnitude), min_freq=f32(pf - q), max_freq=f32(pf + q),
+                duration=f32(ev.duration_s), end_sample=fft_samples_to_raw(ev.length, fsr, sample_rate))
+
+
+def bolid_csv_line(file_basename: str, fields: dict) -> str:
+    """A line of the hourly *_meta.csv (header "# file name; noise; peak f.; mag.; duration")."""
+    return "%s;%s;%s;%s;%s" % (file_basename, _g(fields["noise"]), _g(fields["peak_freq"]), _g(fields["magnitude"]),
+                               _g(fields["duration"]))
+
+
+def met_line(t_sec: int, t_usec: int, fields: dict) -> str:
+    """The stdout line station tooling parses: met;[<s>s, <us>us];noise;peak;mag;fmin;fmax;duration;end#"""
+    return "met;[%ds, %dus];%s;%s;%s;%s;%s;%s;%d#" % (
+        t_sec, t_usec, _g(fields["noise"]), _g(fields["peak_freq"]), _g(fields["magnitude"]), _g(fields["min_freq"]),
+        _g(fields["max_freq"]), _g(fields["duration"]), fields["end_sample"])

@@ -171,3 +171,36 @@ def test_shards_equal_the_whole_on_the_gpu(bins, overlap, world):
     assert np.array_equal(rows, whole_rows)
     for k in ("noise", "peak", "avg"):
         assert np.array_equal(det[k], whole_det[k])
+
+
+@pytest.mark.parametrize("name", ["n2048", "c2b_16k"])
+def test_event_text_formats_match_the_reference_output(name):
+    """8f N4: the CSV metadata lines and the stdout `met;` lines the reference printed for the golden
+    run, rebuilt from the trigger's events (file names and the wall-clock stamp taken from the golden)."""
+    gold = load_golden(name)
+    rec, keys, m = _oracle_bolid(gold)
+    sr, bins, ov = m["sample_rate"], m["bins"], m["overlap"]
+    b = A.bolid_bands(sr, bins, ov, **keys)
+    npa = gold["npa"]
+    from radio_observer_b200.capi import DET_DTYPE
+    n_rows = m["rows"]
+    recs = np.zeros(n_rows, dtype=DET_DTYPE)
+    recs["noise"], recs["avg"] = npa["noise"][:n_rows], npa["mag"][:n_rows]
+    recs["peak"] = [R.frequency_to_bin(f, sr, bins) - b["det_lo"] for f in npa["peakfreq"][:n_rows]]
+    trig = A.BolidTrigger(det_lo=b["det_lo"], advance=b["advance"], jitter=b["jitter"], fft_sample_rate=A.fft_sample_rate(sr, bins, ov))
+    trig.feed(recs)
+    csv = [v["text"] for k, v in gold["fits"].items() if k.endswith(".csv") and "_blid.fits" in v["text"]][0]
+    csv_lines = [l for l in csv.strip().split("\n") if "_blid.fits" in l]
+    met_lines = [l for l in m["stdout"].strip().split("\n") if l.startswith("met;")]
+    dump = [l.split(";") for l in gold["bolid"].strip().split("\n") if l]
+    assert len(trig.events) == len(csv_lines) == len(met_lines) == len(dump) >= 1
+    for ev, cl, ml, d in zip(trig.events, csv_lines, met_lines, dump):
+        f = A.event_fields(ev, sample_rate=sr, bins=bins, overlap=ov, low_detect_freq=keys["low_detect_freq"],
+                           hi_detect_freq=keys["hi_detect_freq"])
+        assert A.bolid_csv_line(cl.split(";")[0], f) == cl
+        stamp = ml.split(";")[1]                                   # "[<s>s, <us>us]": WFTime::now(), not an output of the path
+        ts, tu = int(stamp[1:].split("s,")[0]), int(stamp.split(",")[1].strip()[:-3])
+        assert A.met_line(ts, tu, f) == ml
+        # the BolidMessage fields at full precision
+        assert [np.float32(x) for x in d[:5]] == [f["noise"], f["peak_freq"], f["magnitude"], f["min_freq"], f["max_freq"]]
+        assert int(d[6]) == f["end_sample"]
