@@ -11,9 +11,10 @@ from .capi import (  # noqa: F401
 )
 
 from . import archive  # noqa: F401,E402  (time-sharded archive reprocessing, host-side trigger state machine)
+from . import fits, recorders  # noqa: F401,E402  (archive path: FITS writer, snapshot / bolid file planning)
 
 __all__ = [
-    "archive",
+    "archive", "fits", "recorders",
     "RoError", "WfConfig", "DetRec", "Waterfall", "load_library", "library_path",
     "window_table", "twiddle_table", "IN_INT16", "IN_FLOAT32", "IN_COMPLEX64", "PREC_FP32", "PREC_FP64",
 ]

@@ -1,0 +1,136 @@
+"""recorders.py -- the sequential, O(1)-per-row remainder of the recorders for the ARCHIVE path
+(8e "sequential remainder"): which rows go into which FITS file, under
+which name and with which time stamp.  The streaming path does not use this: there the reference's own
+SnapshotRecorder / BolidRecorder run unmodified behind the adapter.
+
+Everything is expressed in GLOBAL row numbers (row k = frame k of the archive).  The reference works
+on a ring of rows and a table of per-row handles; as long as the ring is not overrun between the moment
+a snapshot is planned and the moment it is written -- it is sized 8 x the longest snapshot for that
+reason (reference src/WaterfallBackend.cpp:339-347) -- ring indices and global rows are the same thing,
+with two quirks kept:
+  * the handle of row r is stored at ring index r+1 (RingBuffer2D::push post-increments, reference
+    src/RingBuffer.h:482-509, src/WaterfallBackend.cpp:507), so the time a snapshot starting at row s
+    is named and stamped with is the time of row s-1 -- and WFTime(0, 0) when s <= 0, the slot never
+    having been written (src/WaterfallBackend.cpp:42-46);
+  * a bolid snapshot may start before row 0 (start = first detecting row + 1 - advance).
+"""
+import math
+from dataclasses import dataclass
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import archive as A
+from . import fits as F
+
+f32 = np.float32
+US = 1000000
+
+
+# ---------------------------------------------------------------------------
+# A7  stream time of a sample: WFTime::addSamples / add (reference src/WFTime.h:85-119)
+# ---------------------------------------------------------------------------
+def _add_samples(t: Tuple[int, int], count: int, sample_rate: int) -> Tuple[int, int]:
+    sec, rem = divmod(int(count), int(sample_rate))
+    micro = int((float(rem) / float(sample_rate)) * float(US))          # truncation toward zero
+    usec = t[1] + micro % US
+    s = t[0] + sec + micro // US + usec // US
+    return (s, usec % US)
+
+
+def frame_times(n_frames: int, bins: int, overlap: int, sample_rate: int, block: int = 1024,
+                t0: Tuple[int, int] = (0, 0)) -> List[Tuple[int, int]]:
+    """Time of the first sample of every frame as the reference derives it: the frontend stamps each
+    block of `block` samples with t0.addSamples(block offset) (src/Frontend.cpp:47-52; 1024 for WAV,
+    4096 for raw TCP), FFTBackend::process re-bases that stamp with addSamples(consumed) after every
+    window it completes inside the block and adds the sample's index within the current stretch
+    (src/FFTBackend.cpp:208-256); every addSamples truncates to whole microseconds."""
+    ov = A.clamp_overlap(bins, overlap)
+    hop = bins - ov
+    out = []
+    for k in range(n_frames):
+        s = k * hop                                   # global index of the frame's first sample
+        b0 = (s // block) * block
+        t = _add_samples(t0, b0, sample_rate)
+        pos = b0
+        # windows that complete inside this block before sample s: frame j is complete once sample
+        # j*hop + bins - 1 is in, i.e. the stretch ends at e_j = j*hop + bins
+        j = max(0, -(-(b0 + 1 - bins) // hop))        # first j with e_j > b0
+        while True:
+            e = j * hop + bins
+            if e > s or e > b0 + block:
+                break
+            t = _add_samples(t, e - pos, sample_rate)
+            pos = e
+            j += 1
+        out.append(_add_samples(t, s - pos, sample_rate))
+    return out
+
+
+# ---------------------------------------------------------------------------
+# A10  snapshot slicing (reference src/WaterfallBackend.cpp:107-127, 339-347, 364-427)
+# ---------------------------------------------------------------------------
+@dataclass
+class PlannedFile:
+    kind: str                    # output_type ("snap", "blid")
+    start_row: int               # global row of the first pixel row (may be < 0 for a bolid)
+    length: int                  # rows
+    time: Tuple[int, int]        # (sec, usec) used for the name, DATE-OBS and CRVAL2
+    file_name: str
+    event: Optional[A.BolidEvent] = None
+
+
+def snapshot_rows(snapshot_length: float, fsr: np.float32) -> int:
+    """max(1, ceil(snapshot_length * fftSampleRate)) in float arithmetic (:339-347)."""
+    return max(1, int(math.ceil(f32(f32(int(snapshot_length)) * f32(fsr)))))
+
+
+def _stamp(times: Sequence[Tuple[int, int]], start_row: int) -> Tuple[int, int]:
+    return times[start_row - 1] if start_row >= 1 else (0, 0)
+
+
+def plan_snapshots(n_rows: int, times: Sequence[Tuple[int, int]], *, sample_rate: int, bins: int, overlap: int,
+                   snapshot_length: float, origin: str, output_type: str = "snap") -> List[PlannedFile]:
+    """SnapshotRecorder: a file of snapshotRows rows whenever that many + 2 rows are waiting, and the
+    unfinished rest at endStream."""
+    fsr = A.fft_sample_rate(sample_rate, bins, A.clamp_overlap(bins, overlap))
+    S = snapshot_rows(snapshot_length, fsr)
+    out, start = [], 0
+    for pushed in range(1, n_rows + 1):                # update() after every row
+        if pushed - start >= S + 2:
+            t = _stamp(times, start)
+            out.append(PlannedFile(output_type, start, S, t, F.file_basename(t[0], t[1], origin, output_type)))
+            start += S
+    if n_rows > start:                                 # stop(): write_unfinished
+        t = _stamp(times, start)
+        out.append(PlannedFile(output_type, start, min(S, n_rows - start), t,
+                               F.file_basename(t[0], t[1], origin, output_type)))
+    return out
+
+
+def plan_bolids(events: Sequence[A.BolidEvent], times: Sequence[Tuple[int, int]], *, sample_rate: int, bins: int,
+                overlap: int, snapshot_length: float, origin: str, output_type: str = "blid") -> List[PlannedFile]:
+    """BolidRecorder: one file per event, named at the first detection with the stamp of its start row,
+    length capped to snapshotRows when it is written (src/BolidRecorder.cpp:171-180, :112-116)."""
+    fsr = A.fft_sample_rate(sample_rate, bins, A.clamp_overlap(bins, overlap))
+    S = snapshot_rows(snapshot_length, fsr)
+    out = []
+    for ev in events:
+        t = _stamp(times, ev.start_row)
+        out.append(PlannedFile(output_type, ev.start_row, min(S, ev.length), t,
+                               F.file_basename(t[0], t[1], origin, output_type), ev))
+    return out
+
+
+def write_planned(path: str, plan: PlannedFile, band_rows: np.ndarray, *, left_bin: int, sample_rate: int, bins: int,
+                  overlap: int, low_freq: float, origin: str, git_version: str = "", local_time: str = "") -> None:
+    """One FITS file: band_rows[r] is global row r cropped to [left_bin, left_bin + width)."""
+    if plan.start_row < 0:
+        raise ValueError("rows before the start of the archive are not available")
+    px = band_rows[plan.start_row:plan.start_row + plan.length]
+    cards = F.snapshot_cards(px.shape[1], px.shape[0], origin=origin, time_sec=plan.time[0], time_usec=plan.time[1],
+                             fft_sample_rate=A.fft_sample_rate(sample_rate, bins, A.clamp_overlap(bins, overlap)),
+                             left_frequency=f32(low_freq),
+                             bin_width=A.bin_to_frequency(1, sample_rate, bins) - A.bin_to_frequency(0, sample_rate, bins),
+                             git_version=git_version, local_time=local_time)
+    F.write_image(path, cards, px)

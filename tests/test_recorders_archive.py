@@ -1,0 +1,86 @@
+"""radio_observer_b200.recorders: frame times, snapshot slicing and bolid files of the archive path
+against the oracle's models (pinned to the reference by test_oracle_golden) and against the names,
+lengths and header cards of the files the reference itself wrote for the golden runs."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import ref_numpy as R
+from radio_observer_b200 import archive as A
+from radio_observer_b200 import recorders as P
+from radio_observer_b200 import fits as F
+from radio_observer_b200.capi import DET_DTYPE
+from helpers import load_golden, recorder_cfg
+
+SKIP = ("DATE    =", "COMMENT Local time", "COMMENT Git version")
+
+
+@pytest.mark.parametrize("bins,overlap,sr,block,n", [
+    (16384, 12288, 96000, 1024, 768000), (2048, 1024, 48000, 1024, 200000), (32768, 24576, 48000, 1024, 400000),
+    (4096, 2048, 192000, 4096, 300000), (1024, 1000, 44100, 1024, 30000), (4096, 0, 96000, 1000, 100000),
+])
+def test_frame_times_follow_the_reference_chain(bins, overlap, sr, block, n):
+    want = R.frame_times(n, bins, overlap, sr, block=block)
+    got = P.frame_times(len(want), bins, overlap, sr, block=block)
+    assert [(t.sec, t.usec) for t in want] == got
+    # and with a stream start time
+    t0 = R.WFTime(1700000000, 999999)
+    want = R.frame_times(n, bins, overlap, sr, block=block, t0=t0)
+    assert [(t.sec, t.usec) for t in want] == P.frame_times(len(want), bins, overlap, sr, block=block, t0=(1700000000, 999999))
+
+
+@pytest.mark.parametrize("name", ["n2048", "c2b_16k"])
+def test_planned_files_match_what_the_reference_wrote(name, tmp_path):
+    g = load_golden(name)
+    m = g["meta"]
+    sr, bins, ov, n_rows = m["sample_rate"], m["bins"], m["overlap"], m["rows"]
+    snap, bol = recorder_cfg(g, "snapshot"), recorder_cfg(g, "bolid")
+    times = P.frame_times(n_rows, bins, ov, sr, block=1024)
+    # --- snapshot recorder
+    plan = P.plan_snapshots(n_rows, times, sample_rate=sr, bins=bins, overlap=ov,
+                            snapshot_length=snap["snapshot_length"], origin="gold")
+    want_names = sorted(k for k in g["fits"] if k.endswith("_snap.fits"))
+    assert [p.file_name for p in plan] == want_names
+    lo, hi = A.frequency_to_bin(snap["low_freq"], sr, bins), A.frequency_to_bin(snap["hi_freq"], sr, bins)
+    b0, b1 = m["band"]
+    band_rows = g["bands"][:, lo - b0:hi - b0]
+    import hashlib
+    for p in plan:
+        want = g["fits"][p.file_name]
+        assert want["shape"] == [hi - lo, p.length]
+        path = str(tmp_path / p.file_name)
+        P.write_planned(path, p, band_rows, left_bin=lo, sample_rate=sr, bins=bins, overlap=ov,
+                        low_freq=snap["low_freq"], origin="gold")
+        cards, hdr, data = F.read_image(path)
+        assert [c for c in cards if not c.startswith(SKIP)] == [c for c in want["cards"] if not c.startswith(SKIP)]
+        assert hashlib.sha256(np.ascontiguousarray(data).tobytes()).hexdigest() == want["sha256"]
+    # --- bolid recorder, driven by the reference's own per-row records
+    keys = {k: bol[k] for k in ("low_detect_freq", "hi_detect_freq", "low_noise_freq", "hi_noise_freq",
+                                "advance_time", "jitter_time", "avg_freq_range")}
+    b = A.bolid_bands(sr, bins, ov, **keys)
+    npa = g["npa"]
+    recs = np.zeros(n_rows, dtype=DET_DTYPE)
+    recs["noise"], recs["avg"] = npa["noise"][:n_rows], npa["mag"][:n_rows]
+    recs["peak"] = [R.frequency_to_bin(f, sr, bins) - b["det_lo"] for f in npa["peakfreq"][:n_rows]]
+    trig = A.BolidTrigger(det_lo=b["det_lo"], advance=b["advance"], jitter=b["jitter"], fft_sample_rate=A.fft_sample_rate(sr, bins, ov))
+    trig.feed(recs)
+    bplan = P.plan_bolids(trig.events, times, sample_rate=sr, bins=bins, overlap=ov,
+                          snapshot_length=bol["snapshot_length"], origin="gold")
+    want_names = sorted(k for k in g["fits"] if k.endswith("_blid.fits"))
+    assert sorted(p.file_name for p in bplan) == want_names
+    blo, bhi = A.frequency_to_bin(bol["low_freq"], sr, bins), A.frequency_to_bin(bol["hi_freq"], sr, bins)
+    bband = g["bands"][:, blo - b0:bhi - b0]
+    n_px = 0
+    for p in bplan:
+        want = g["fits"][p.file_name]
+        assert want["shape"] == [bhi - blo, p.length]
+        if p.start_row < 0:
+            continue                                   # rows before the archive: the reference wrote ring garbage there
+        path = str(tmp_path / p.file_name)
+        P.write_planned(path, p, bband, left_bin=blo, sample_rate=sr, bins=bins, overlap=ov, low_freq=bol["low_freq"], origin="gold")
+        cards, hdr, data = F.read_image(path)
+        assert [c for c in cards if not c.startswith(SKIP)] == [c for c in want["cards"] if not c.startswith(SKIP)]
+        assert hashlib.sha256(np.ascontiguousarray(data).tobytes()).hexdigest() == want["sha256"]
+        n_px += 1
+    assert n_px >= 1

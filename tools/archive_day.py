@@ -35,6 +35,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--hours", type=float, default=1.0)
     ap.add_argument("--dir", default="/dev/shm" if os.path.isdir("/dev/shm") else "/tmp")
+    ap.add_argument("--out", default=None, help="write the snapshot / bolid FITS files and the metadata CSV here")
+    ap.add_argument("--max-files", type=int, default=200, help="bound on FITS files written per recorder")
     a = ap.parse_args()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -88,13 +90,33 @@ def main():
             r2, d2 = compute(np.ascontiguousarray(iq[2 * f0 * hop:2 * ((f1 - 1) * hop + BINS)]))
             seams_ok = seams_ok and np.array_equal(r2, rows[f0:f1]) and np.array_equal(d2["peak"], det["peak"][f0:f1]) \
                 and np.array_equal(d2["noise"], det["noise"][f0:f1])
+        written = None
+        if a.out:
+            from radio_observer_b200 import recorders as P
+            os.makedirs(a.out, exist_ok=True)
+            t2 = time.time()
+            times = P.frame_times(int(F), BINS, OVERLAP, SR, block=1024)
+            common = dict(sample_rate=SR, bins=BINS, overlap=OVERLAP, origin="archive")
+            snaps = P.plan_snapshots(int(F), times, snapshot_length=60, **common)
+            blids = [p for p in P.plan_bolids(trig.events, times, snapshot_length=60, **common) if p.start_row >= 0]
+            with open(os.path.join(a.out, "archive_meta.csv"), "w") as csv:
+                csv.write("# file name; noise; peak f.; mag.; duration\n")
+                for p in blids:
+                    f = A.event_fields(p.event, sample_rate=SR, bins=BINS, overlap=OVERLAP,
+                                       low_detect_freq=KEYS["low_detect_freq"], hi_detect_freq=KEYS["hi_detect_freq"])
+                    csv.write(A.bolid_csv_line(p.file_name, f) + "\n")
+            for p in snaps[:a.max_files] + blids[:a.max_files]:
+                P.write_planned(os.path.join(a.out, p.file_name), p, rows, left_bin=band[0], low_freq=26200.0, **common)
+            written = {"snapshots_planned": len(snaps), "bolids_planned": len(blids),
+                       "fits_written": min(len(snaps), a.max_files) + min(len(blids), a.max_files),
+                       "seconds": round(time.time() - t2, 2)}
         line = {"tool": "archive_day", "hours": a.hours, "n_gpus": world, "samples": n_total, "frames": int(F),
                 "bins": BINS, "overlap": OVERLAP, "seconds_compute_and_merge": round(t_all, 3),
                 "Msamples_per_s_end_to_end": round(n_total / t_all / 1e6, 1),
                 "realtime_factor": round(a.hours * 3600 / t_all, 1),
                 "events": len(trig.events), "seconds_trigger_fsm": round(t_trig, 3),
                 "seams_bit_identical": bool(seams_ok), "shards": [[s.frame0, s.frame1] for s in shards],
-                "seconds_generate_archive": round(t_gen, 1),
+                "seconds_generate_archive": round(t_gen, 1), "outputs": written,
                 "note": "host int16 archive in shared memory -> per-rank ro_wf_process_host -> rows of the recorder band + "
                         "detector records gathered on rank 0 (gloo); no data-path collective"}
         os.write(out_fd, (json.dumps(line) + "\n").encode())
