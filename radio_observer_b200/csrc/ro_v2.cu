@@ -70,9 +70,14 @@ bool v2_pick(int log2n, int mode, bool gain, V2Kernel *out)
 	}
 	switch (log2n) {
 #ifndef RO_EXP_ONLY14
-	case 10: return pick_one<10, 16, 4, 12, 12>(mode, gain, out);
-	case 11: return pick_one<11, 16, 8, 6, 6>(mode, gain, out);
-	case 12: return pick_one<12, 16, 16, 3, 3>(mode, gain, out);
+#ifndef RO_MINB10
+#define RO_MINB10 12
+#define RO_MINB11 6
+#define RO_MINB12 3
+#endif
+	case 10: return pick_one<10, 16, 4, RO_MINB10, RO_MINB10>(mode, gain, out);
+	case 11: return pick_one<11, 16, 8, RO_MINB11, RO_MINB11>(mode, gain, out);
+	case 12: return pick_one<12, 16, 16, RO_MINB12, RO_MINB12>(mode, gain, out);
 	case 13: return pick_one<13, 32, 8, 2, 2>(mode, gain, out);
 #endif
 	case 14: return pick_one<14, 32, 16, 1, 1>(mode, gain, out);
