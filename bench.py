@@ -200,7 +200,7 @@ def host_station_iq(n_samples, seed):
     return synth.generate_int16(spec)
 
 
-def run_reference_cpu(sample_seconds, procs, binary=None, factory="waterfall", extra=None, wav_path=None):
+def run_reference_cpu(sample_seconds, procs, binary=None, factory="waterfall", extra=None, wav_path=None, flags=()):
     """Time the reference's own C++ classes (or, if the binary is absent, the numpy port)
     on `procs` independent time shards of sample_seconds each.  Returns
     (Msamples/s, kind, cores, description).  With binary=CUDA_BIN, factory="waterfall_cuda" the
@@ -228,7 +228,7 @@ def run_reference_cpu(sample_seconds, procs, binary=None, factory="waterfall", e
                 # constructor) and sometimes aborts before processing: retry
                 for attempt in range(25):
                     t0 = time.perf_counter()
-                    rc = subprocess.call([binary, "-c", os.path.join(d, "cfg.json"), "-q", wav],
+                    rc = subprocess.call([binary, "-c", os.path.join(d, "cfg.json"), "-q", *flags, wav],
                                          stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, cwd=d)
                     if rc == 0:
                         times[p] = time.perf_counter() - t0
@@ -460,6 +460,15 @@ def main():
                 dropin = {"value": r[0], "unit": "Msamples/s", "cores": 1,
                           "what": "reference Pipeline/WAVStream/recorders unmodified, backend factory waterfall_cuda "
                                   "(cuda_batch_frames 64), same %.0f s WAV and outputs as cpu_baseline" % secs}
+            # the same again with the narrow-ingest frontend: NarrowWAVStream hands the int16
+            # blocks of the file to CudaWaterfallBackend::processRaw, 4 B per sample from the file to the GPU
+            r = run_reference_cpu(secs, 1, binary=CUDA_BIN, factory="waterfall_cuda",
+                                  extra={"cuda_batch_frames": 64}, wav_path=wav, flags=("-N",)) if wav else None
+            if r is not None and dropin is not None:
+                dropin["narrow_ingest"] = {
+                    "value": r[0], "unit": "Msamples/s", "cores": 1,
+                    "what": "as above with the frontend NarrowWAVStream -> processRaw(int16) instead of WAVStream -> "
+                            "process(vector<Complex>); recorders, FITS and CSV output unchanged"}
         finally:
             shutil.rmtree(wtmp, ignore_errors=True)
 

@@ -13,10 +13,11 @@
  *     that capture the detector's per-row (noise, peakFreq, magnitude) and
  *     the emitted bolid events.
  *
- * usage: ref_oracle -c CONFIG.json [-n NAME] [-d DUMPDIR] [-r] [-q] WAV_FILE
+ * usage: ref_oracle -c CONFIG.json [-n NAME] [-d DUMPDIR] [-r] [-q] [-N] WAV_FILE
  *   -d DUMPDIR  write rowinfo.bin / noise.bin / bolid.txt / timing.json there
  *   -r          also write every full row to DUMPDIR/rows.f32
  *   -q          quiet (log warnings and errors only, to stderr)
+ *   -N          (adapter build only) read the WAV with NarrowWAVStream instead of WAVStream
  */
 #include <cstdio>
 #include <cstdlib>
@@ -33,6 +34,11 @@ using namespace cppapp;
 #include "BolidRecorder.h"
 #include "BolidMessage.h"
 #include "MessageDispatch.h"
+#ifdef RO_NARROW_FRONTEND
+/* only in the adapter build (radio_observer_b200/host/Makefile): -N selects the narrow-ingest
+ * frontend instead of the reference's WAVStream */
+#include "NarrowWAVStream.h"
+#endif
 
 struct RowInfo {
 	int32_t  mark;      /* buffer_->mark() after the push = index of the NEXT row */
@@ -116,7 +122,7 @@ static double nowSeconds()
 int main(int argc, char **argv)
 {
 	std::string configFile, cfgName, dumpDir, wavFile;
-	bool dumpRows = false, quiet = false;
+	bool dumpRows = false, quiet = false, narrow = false;
 	for (int i = 1; i < argc; i++) {
 		std::string a = argv[i];
 		if (a == "-c" && i + 1 < argc) configFile = argv[++i];
@@ -124,6 +130,7 @@ int main(int argc, char **argv)
 		else if (a == "-d" && i + 1 < argc) dumpDir = argv[++i];
 		else if (a == "-r") dumpRows = true;
 		else if (a == "-q") quiet = true;
+		else if (a == "-N") narrow = true;
 		else wavFile = a;
 	}
 	if (configFile.empty() || wavFile.empty()) {
@@ -172,7 +179,16 @@ int main(int argc, char **argv)
 	addListener<NoiseMessage>(onNoise, NULL);
 	addListener<BolidMessage>(onBolid, NULL);
 
-	pipeline->setFrontend(new WAVStream(new FileInput(wavFile)));
+	if (narrow) {
+#ifdef RO_NARROW_FRONTEND
+		pipeline->setFrontend(new NarrowWAVStream(new FileInput(wavFile)));
+#else
+		fprintf(stderr, "-N: this build has no narrow-ingest frontend\n");
+		return 2;
+#endif
+	} else {
+		pipeline->setFrontend(new WAVStream(new FileInput(wavFile)));
+	}
 
 	double t0 = nowSeconds();
 	pipeline->run();

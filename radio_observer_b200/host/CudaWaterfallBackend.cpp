@@ -30,6 +30,7 @@ CudaWaterfallBackend::CudaWaterfallBackend(int bins, int overlap, std::string or
 	iqGain_(0), iqPhaseShift_(0),
 	wf_(NULL), failed_(false),
 	fill_(0),
+	inFormat_(RO_IN_COMPLEX64), samplesIn_(0),
 	delivered_(0)
 {
 	if (overlap_ < 0) overlap_ = 0;
@@ -72,23 +73,48 @@ void CudaWaterfallBackend::startStream(StreamInfo info)
 	delivered_ = 0;
 	failed_ = false;
 
+	samplesIn_ = 0;
+	// the Pipeline's frontends hand over vector<Complex>; a narrow frontend switches the format with
+	// its first processRaw()
+	createHandle(RO_IN_COMPLEX64);
+}
+
+
+bool CudaWaterfallBackend::createHandle(int inFormat)
+{
 	if (wf_) { ro_wf_destroy(wf_); wf_ = NULL; }
 	ro_wf_config cfg;
 	memset(&cfg, 0, sizeof cfg);
 	cfg.bins = bins_;
 	cfg.overlap = overlap_;
-	cfg.sample_rate = info.sampleRate;
-	cfg.in_format = RO_IN_COMPLEX64;          // the Pipeline hands over vector<Complex>
+	cfg.sample_rate = streamInfo_.sampleRate;
+	cfg.in_format = inFormat;
 	cfg.iq_gain = getGain();
 	cfg.iq_phase_shift = getPhaseShift();
 	cfg.n_bands = 0;                          // recorders slice the full row themselves
 	cfg.device = device_;
 	cfg.max_batch_frames = batchFrames_;
 	cfg.precision = precision_;
+	inFormat_ = inFormat;
 	if (ro_wf_create(&cfg, &wf_) != RO_OK) {
 		wf_ = NULL;
 		fail("ro_wf_create");
+		return false;
 	}
+	return true;
+}
+
+
+bool CudaWaterfallBackend::ensureFormat(int inFormat)
+{
+	if (inFormat_ == inFormat) return true;
+	if (samplesIn_ > 0) {
+		// one stream, one encoding: the device-side sample ring holds what was pushed so far
+		LOG_ERROR("CudaWaterfallBackend: process() and processRaw() mixed within one stream");
+		failed_ = true;
+		return false;
+	}
+	return createHandle(inFormat);
 }
 
 
@@ -111,13 +137,71 @@ void CudaWaterfallBackend::pushSamples(const Complex *src, int count, WFTime tim
 }
 
 
+void CudaWaterfallBackend::pushSamples(const int16_t *src, int count, WFTime timeOffset)
+{
+	// Same effects as the Complex overload on the widened block, without a per-sample step.
+	// Handles: sample i of this run starts a frame when i = toNextHop_ (mod hop); the ring mark after
+	// its push is the mark before the run + i + 1, wrapped (src/RingBuffer.h:289-290).
+	const int hop = bins_ - overlap_;
+	const int cap = rawBuffer_.capacity_;
+	{
+		const long mark0 = rawBuffer_.mark();
+		int i = toNextHop_;
+		for (; i < count; i += hop) {
+			hopHandles_.push_back(RawDataHandle(
+				(int)((mark0 + i + 1) % cap),
+				timeOffset.addSamples(i, streamInfo_.sampleRate)
+			));
+		}
+		toNextHop_ = i - count;
+	}
+
+	// Raw I/Q ring: (float)(double)int16 = (float)int16, exactly what floatToInt(Complex, float*)
+	// stores (src/FFTBackend.h:250-254); rows of one chunk are contiguous (src/RingBuffer.h:257-259)
+	int done = 0;
+	while (done < count) {
+		const int index = rawBuffer_.head_.index;
+		int run = rawBuffer_.chunkRows_ - index % rawBuffer_.chunkRows_;
+		if (run > count - done) run = count - done;
+		float *dst = rawBuffer_.head_.item;
+		const int16_t *s = src + 2 * (size_t)done;
+		for (int j = 0; j < 2 * run; j++) dst[j] = (float)s[j];
+		rawBuffer_.head_ = IQBuffer::ChunkItem(rawBuffer_, (index + run) % cap,
+		                                       rawBuffer_.head_.generation + run);
+		rawBuffer_.size_ = rawBuffer_.size_ + run < cap ? rawBuffer_.size_ + run : cap;
+		done += run;
+	}
+
+	if (ro_wf_push(wf_, src, (size_t)count) != RO_OK) fail("ro_wf_push");
+}
+
+
 void CudaWaterfallBackend::process(const std::vector<Complex> &data, DataInfo info)
 {
 	if (failed_ || !wf_ || data.empty()) return;
+	if (!ensureFormat(RO_IN_COMPLEX64)) return;
+	processSamples(&(data[0]), (int)data.size(), info);
+}
 
-	int size = data.size();
-	const Complex *src = &(data[0]);
+
+void CudaWaterfallBackend::processRaw(const int16_t *iq, int count, DataInfo info)
+{
+	if (failed_ || !wf_ || count <= 0) return;
+	if (!ensureFormat(RO_IN_INT16)) return;
+	processSamples(iq, count, info);
+}
+
+
+template<class S> static inline const S *advanceSamples(const S *p, int n);
+template<> inline const Complex *advanceSamples<Complex>(const Complex *p, int n) { return p + n; }
+template<> inline const int16_t *advanceSamples<int16_t>(const int16_t *p, int n) { return p + 2 * (size_t)n; }
+
+
+template<class S>
+void CudaWaterfallBackend::processSamples(const S *src, int size, DataInfo info)
+{
 	WFTime timeOffset = info.timeOffset;
+	samplesIn_ += size;
 
 	while (size >= (bins_ - fill_)) {
 		int count = bins_ - fill_;
@@ -135,7 +219,7 @@ void CudaWaterfallBackend::process(const std::vector<Complex> &data, DataInfo in
 
 		fill_ = overlap_;
 		size -= count;
-		src += count;
+		src = advanceSamples<S>(src, count);
 
 		timeOffset = timeOffset.addSamples(count, streamInfo_.sampleRate);
 		info_.offset++;

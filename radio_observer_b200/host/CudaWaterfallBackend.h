@@ -13,6 +13,10 @@
  * Selecting it is one string in the JSON config:  "factory": "waterfall_cuda"
  * (same keys as "waterfall", src/WaterfallBackend.cpp:620-644, plus the optional
  * keys cuda_device (0), cuda_batch_frames (1) and cuda_precision (0 = FP32, 1 = FP64)).
+ *
+ * Narrow ingest: processRaw() takes the interleaved int16 I/Q of a WAV block as it
+ * lies in the file (4 B per sample instead of a 16 B Complex, src/WAVStream.cpp:115-121) with the
+ * same DataInfo Frontend::process would pass; NarrowWAVStream.h is the frontend that calls it.
  */
 #ifndef CUDA_WATERFALL_BACKEND_H
 #define CUDA_WATERFALL_BACKEND_H
@@ -22,10 +26,22 @@
 
 // Everything WaterfallBackend.h includes, first and untouched ...
 #include <cmath>
+#include <cfloat>
+#include <limits>
 #include <fitsio.h>
+#include <fftw3.h>
+#include "Backend.h"
+// RingBuffer2D with its private section readable as well: the narrow-ingest path (processRaw) fills
+// the raw I/Q ring a run of samples at a time and then moves the head by the run length, which needs
+// head_ / size_ / chunkRows_ (src/RingBuffer.h:222-306); the per-sample push() it replaces costs an
+// integer division per sample (src/RingBuffer.h:289-290).  No reservation is ever made on the raw
+// ring (only on the row ring, src/WaterfallBackend.cpp:118), so push()'s reservation scan has
+// nothing to mark there.
+#define private public
+#include "RingBuffer.h"
+#undef private
 #include "FFTBackend.h"
 #include "FITSWriter.h"
-#include "RingBuffer.h"
 #include "Channel.h"
 #include "BolidMessage.h"
 #include "CsvLog.h"
@@ -72,7 +88,14 @@ private:
 
 	std::vector<float>           rows_;      // harvested rows, bins_ floats each
 
+	int     inFormat_;         // RO_IN_* the handle was created for
+	long    samplesIn_;        // samples accepted since startStream
+
+	bool createHandle(int inFormat);
+	bool ensureFormat(int inFormat);
 	void pushSamples(const Complex *src, int count, WFTime timeOffset);
+	void pushSamples(const int16_t *src, int count, WFTime timeOffset);
+	template<class S> void processSamples(const S *src, int size, DataInfo info);
 	void harvest(bool flush, int atMost = 0);
 	void fail(const char *what);
 
@@ -84,6 +107,11 @@ public:
 	virtual void startStream(StreamInfo info);
 	virtual void process(const std::vector<Complex> &data, DataInfo info);
 	virtual void endStream();
+
+	/// Backend::process for samples still in the WAV file's encoding: `count` complex samples as
+	/// interleaved int16 [I, Q], unscaled (what src/WAVStream.cpp:115-121 widens to Complex).
+	/// Same frames, rows, handles and recorder calls as process() on the widened block.
+	void processRaw(const int16_t *iq, int count, DataInfo info);
 
 	/// number of rows delivered to the recorders so far
 	long deliveredRows() const { return delivered_; }

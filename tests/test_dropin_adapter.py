@@ -35,8 +35,8 @@ ROWINFO = np.dtype([("mark", "<i4"), ("rawmark", "<i4"), ("sec", "<i8"), ("usec"
 NPA = np.dtype([("noise", "<f4"), ("peakfreq", "<f4"), ("mag", "<f4")])
 
 
-def run_pipeline(binary, g, factory, tmp, extra=None):
-    d = os.path.join(tmp, factory)
+def run_pipeline(binary, g, factory, tmp, extra=None, flags=(), tag=None, iq=None):
+    d = os.path.join(tmp, tag or factory)
     os.makedirs(os.path.join(d, "OUT"))
     os.makedirs(os.path.join(d, "dump"))
     cfg = json.loads(json.dumps(g["config"]))
@@ -47,14 +47,14 @@ def run_pipeline(binary, g, factory, tmp, extra=None):
     open(os.path.join(d, "cfg.json"), "w").write(txt)
     wav = os.path.join(tmp, "in.wav")
     if not os.path.exists(wav):
-        synth.write_wav(wav, g["iq"], g["sample_rate"])
+        synth.write_wav(wav, g["iq"] if iq is None else iq, g["sample_rate"])
     # the reference starts recorder threads from a base-class constructor and now and then
     # aborts with "pure virtual method called" before reading any sample: retry
     for attempt in range(25):
         for sub in ("OUT", "dump"):
             shutil.rmtree(os.path.join(d, sub))
             os.makedirs(os.path.join(d, sub))
-        r = subprocess.run([binary, "-c", os.path.join(d, "cfg.json"), "-d", os.path.join(d, "dump"), "-r", "-q", wav],
+        r = subprocess.run([binary, "-c", os.path.join(d, "cfg.json"), "-d", os.path.join(d, "dump"), "-r", "-q", *flags, wav],
                            cwd=d, capture_output=True, text=True)
         if r.returncode == 0:
             break
@@ -99,7 +99,15 @@ def test_cuda_backend_is_a_drop_in(name, batch):
     _retry_reference_races(_dropin_once, name, batch)
 
 
-def _dropin_once(name, batch):
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,batch", [("n2048", 1), ("c2b_16k", 1), ("c2b_16k", 64)])
+def test_narrow_ingest_is_a_drop_in(name, batch):
+    """SURVEY 8f N2: NarrowWAVStream -> CudaWaterfallBackend::processRaw (int16 all the way to the GPU)
+    against the stock WAVStream -> WaterfallBackend, same checks as the Complex path."""
+    _retry_reference_races(_dropin_once, name, batch, True)
+
+
+def _dropin_once(name, batch, narrow=False):
     if not (os.path.exists(REF_BIN) and os.path.exists(CUDA_BIN)):
         pytest.fail("prebuilt binaries missing: run __graft_entry__.build() in the build container")
     g = load_golden(name)
@@ -113,7 +121,8 @@ def _dropin_once(name, batch):
         # thread's date (seen: 19700101000000 + 394 ms instead of 19700101000004 + 394 ms).
         # That race is the reference's; rerun when only the names differ.
         for attempt in range(6):
-            got = run_pipeline(CUDA_BIN, g, "waterfall_cuda", tmp, {"cuda_batch_frames": batch})
+            got = run_pipeline(CUDA_BIN, g, "waterfall_cuda", tmp, {"cuda_batch_frames": batch},
+                               flags=("-N",) if narrow else ())
             if sorted(got["fits"]) == sorted(ref["fits"]):
                 break
             shutil.rmtree(os.path.join(tmp, "waterfall_cuda"))
@@ -212,6 +221,42 @@ def _dropin_fp64_once(name):
             a, b = ref["fits"][fn], got["fits"][fn]
             assert a["shape"] == b["shape"] and a["cards"] == b["cards"], fn
             assert (np.abs(a["data"].astype(np.float64) - b["data"]) <= np.spacing(np.abs(a["data"]))).all(), fn
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
+@pytest.mark.parametrize("tail", [0, 1, 300, 512])
+def test_narrow_wav_frontend_reads_what_wavstream_reads(tail):
+    """The frontend alone, on the CPU: NarrowWAVStream in front of the reference's own stock backend
+    (which gets the widened block) against WAVStream in front of the same backend.  Everything is
+    bit-identical, including the tail block of a data chunk that is not a multiple of 4096 bytes,
+    for which WAVStream passes on twice the samples it read (src/WAVStream.cpp:126-139)."""
+    if not (os.path.exists(REF_BIN) and os.path.exists(CUDA_BIN)):
+        pytest.fail("prebuilt binaries missing: run __graft_entry__.build() in the build container")
+    g = load_golden("n2048")
+    iq = g["iq"]
+    if tail:
+        iq = iq[: 2 * ((len(iq) // 2 // 1024 - 3) * 1024 + tail)]
+    tmp = tempfile.mkdtemp(prefix="ro_narrow_")
+    try:
+        def once():
+            for sub in ("a", "b"):
+                shutil.rmtree(os.path.join(tmp, sub), ignore_errors=True)
+            a = run_pipeline(REF_BIN, g, "waterfall", tmp, tag="a", iq=iq)
+            b = run_pipeline(CUDA_BIN, g, "waterfall", tmp, flags=("-N",), tag="b", iq=iq)
+            assert len(a["rows"]) > 0 and np.array_equal(a["rows"], b["rows"])
+            assert np.array_equal(a["info"], b["info"])
+            assert np.array_equal(a["npa"], b["npa"])
+            assert a["bolid"] == b["bolid"]
+            assert sorted(a["fits"]) == sorted(b["fits"])
+            for fn in a["fits"]:
+                assert a["fits"][fn]["cards"] == b["fits"][fn]["cards"], fn
+                assert np.array_equal(a["fits"][fn]["data"], b["fits"][fn]["data"]), fn
+            if tail:
+                n_in = len(iq) // 2 + tail        # the doubled tail block
+                hop = g["meta"]["bins"] - g["meta"]["overlap"]
+                assert len(a["rows"]) == (n_in - g["meta"]["bins"]) // hop + 1
+        _retry_reference_races(once)
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
 
