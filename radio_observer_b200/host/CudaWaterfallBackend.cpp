@@ -19,6 +19,8 @@
 #include "CudaWaterfallBackend.h"
 
 #include <cstring>
+#include <climits>
+#include <unistd.h>
 
 CudaWaterfallBackend::CudaWaterfallBackend(int bins, int overlap, std::string origin,
                                            int device, int batchFrames, int precision) :
@@ -30,7 +32,7 @@ CudaWaterfallBackend::CudaWaterfallBackend(int bins, int overlap, std::string or
 	iqGain_(0), iqPhaseShift_(0),
 	wf_(NULL), failed_(false),
 	fill_(0),
-	inFormat_(RO_IN_COMPLEX64), samplesIn_(0),
+	inFormat_(RO_IN_COMPLEX64), samplesIn_(0), rawPushed_(0),
 	delivered_(0)
 {
 	if (overlap_ < 0) overlap_ = 0;
@@ -74,6 +76,9 @@ void CudaWaterfallBackend::startStream(StreamInfo info)
 	failed_ = false;
 
 	samplesIn_ = 0;
+	rawPushed_ = 0;
+	resAbs_.clear();
+	resStart_.clear();
 	// the Pipeline's frontends hand over vector<Complex>; a narrow frontend switches the format with
 	// its first processRaw()
 	createHandle(RO_IN_COMPLEX64);
@@ -122,6 +127,8 @@ void CudaWaterfallBackend::pushSamples(const Complex *src, int count, WFTime tim
 {
 	// raw I/Q ring: one push per sample like src/FFTBackend.cpp:218; the handle (ring mark after the
 	// push, stream time of the sample) only where a frame can start
+	waitBeforeRawPush(count);
+	rawPushed_ += count;
 	for (int i = 0; i < count; i++) {
 		floatToInt(src[i], rawBuffer_.push());
 		if (toNextHop_ == 0) {
@@ -144,6 +151,8 @@ void CudaWaterfallBackend::pushSamples(const int16_t *src, int count, WFTime tim
 	// its push is the mark before the run + i + 1, wrapped (src/RingBuffer.h:289-290).
 	const int hop = bins_ - overlap_;
 	const int cap = rawBuffer_.capacity_;
+	waitBeforeRawPush(count);
+	rawPushed_ += count;
 	{
 		const long mark0 = rawBuffer_.mark();
 		int i = toNextHop_;
@@ -251,6 +260,8 @@ void CudaWaterfallBackend::harvest(bool flush, int atMost)
 		for (size_t r = 0; r < n && !pending_.empty(); r++) {
 			// what processFFT does after its magnitude loop (src/WaterfallBackend.cpp:488,507,534-536):
 			// the GPU row is already magnitude, fftshifted, float
+			// this push overwrites absolute row delivered_ - capacity
+			waitForWriters(delivered_ - buffer_.capacity_ + 1);
 			float *row = buffer_.push();
 			memcpy(row, &rows_[r * (size_t)bins_], sizeof(float) * (size_t)bins_);
 			PendingFrame p = pending_.front();
@@ -260,9 +271,74 @@ void CudaWaterfallBackend::harvest(bool flush, int atMost)
 				(*it)->update();
 			}
 			delivered_++;
+			noteReservations();
 		}
 		want -= n < want ? n : want;
 	}
+}
+
+
+void CudaWaterfallBackend::noteReservations()
+{
+	// called on the producer thread right after the recorders' update(): reserve() only ever runs
+	// there (SnapshotRecorder::startWriting, src/WaterfallBackend.cpp:108-121), the writers only free
+	MutexLock lock(&bufferMutex_);
+	const size_t n = buffer_.reservations_.size();
+	if (resAbs_.size() < n) { resAbs_.resize(n, -1); resStart_.resize(n, -1); }
+	const int cap = buffer_.capacity_;
+	const int head = buffer_.mark();             // index of the next row = delivered_ mod capacity
+	for (size_t i = 0; i < n; i++) {
+		if (!buffer_.reservations_[i].alive) { resAbs_[i] = -1; continue; }
+		const int start = buffer_.reservations_[i].start;
+		if (resAbs_[i] != -1 && resStart_[i] == start) continue;
+		const int back = ((head - start) % cap + cap) % cap;   // rows between the snapshot's first row and the head
+		resAbs_[i] = delivered_ - back;          // may be negative: a bolid right after the start of the stream
+		resStart_[i] = start;
+		if (resAbs_[i] == -1) resAbs_[i] = -2;   // keep -1 for "none"
+	}
+}
+
+
+long CudaWaterfallBackend::oldestReservedRow()
+{
+	MutexLock lock(&bufferMutex_);
+	long oldest = LONG_MAX;
+	const size_t n = buffer_.reservations_.size() < resAbs_.size() ? buffer_.reservations_.size() : resAbs_.size();
+	for (size_t i = 0; i < n; i++) {
+		if (resAbs_[i] == -1) continue;
+		if (!buffer_.reservations_[i].alive || buffer_.reservations_[i].start != resStart_[i]) continue;
+		if (resAbs_[i] < oldest) oldest = resAbs_[i];
+	}
+	return oldest;
+}
+
+
+void CudaWaterfallBackend::waitForWriters(long firstNeededRow)
+{
+	// rows below firstNeededRow are about to be lost: wait until no queued snapshot starts there.
+	// A snapshot that old is complete, so its writer does not depend on rows still to come; the
+	// time limit only guards against a writer that died.
+	if (firstNeededRow <= 0 && resAbs_.empty()) return;
+	long waited = 0;
+	while (oldestReservedRow() < firstNeededRow) {
+		usleep(200);
+		waited += 200;
+		if (waited > 60L * 1000 * 1000) {
+			LOG_WARNING("CudaWaterfallBackend: a recorder has not written a snapshot for 60 s; overwriting its rows");
+			break;
+		}
+	}
+}
+
+
+void CudaWaterfallBackend::waitBeforeRawPush(int count)
+{
+	// the raw I/Q of a queued bolid snapshot starts at (or one hop after) the first sample of its
+	// first row: sample row * hop
+	const long hop = bins_ - overlap_;
+	const long firstNeededSample = rawPushed_ + count - rawBuffer_.capacity_;
+	if (firstNeededSample <= 0) return;
+	waitForWriters((firstNeededSample + hop - 1) / hop);
 }
 
 

@@ -90,6 +90,21 @@ private:
 
 	int     inFormat_;         // RO_IN_* the handle was created for
 	long    samplesIn_;        // samples accepted since startStream
+	long    rawPushed_;        // samples pushed to the raw I/Q ring since startStream
+
+	// Back-pressure.  The reference's recorders write their files from worker threads that read the
+	// row ring, its handle table and the raw ring LATER (src/WaterfallBackend.cpp:60-108, :141-258);
+	// a reservation only flags an overwritten region (src/RingBuffer.h:489-493), nothing stops the
+	// producer.  At the reference's own speed the writers keep up; behind this backend a WAV is
+	// consumed several times faster, the producer laps the ring (8 snapshot lengths) and the writer
+	// stores rows, times and file names of one ring capacity later.  So the producer waits before it
+	// overwrites what a queued snapshot still needs: per live reservation the absolute row its
+	// snapshot starts at, noted when the reservation appears.
+	std::vector<long>            resAbs_;    // by reservation handle; -1 = none noted
+	std::vector<int>             resStart_;  // the ring index it was noted for
+	void noteReservations();
+	long oldestReservedRow();
+	void waitForWriters(long firstNeededRow);
 
 	bool createHandle(int inFormat);
 	bool ensureFormat(int inFormat);
@@ -97,6 +112,7 @@ private:
 	void pushSamples(const int16_t *src, int count, WFTime timeOffset);
 	template<class S> void processSamples(const S *src, int size, DataInfo info);
 	void harvest(bool flush, int atMost = 0);
+	void waitBeforeRawPush(int count);
 	void fail(const char *what);
 
 public:

@@ -35,7 +35,7 @@ ROWINFO = np.dtype([("mark", "<i4"), ("rawmark", "<i4"), ("sec", "<i8"), ("usec"
 NPA = np.dtype([("noise", "<f4"), ("peakfreq", "<f4"), ("mag", "<f4")])
 
 
-def run_pipeline(binary, g, factory, tmp, extra=None, flags=(), tag=None, iq=None):
+def run_pipeline(binary, g, factory, tmp, extra=None, flags=(), tag=None, iq=None, dump_rows=True):
     d = os.path.join(tmp, tag or factory)
     os.makedirs(os.path.join(d, "OUT"))
     os.makedirs(os.path.join(d, "dump"))
@@ -54,7 +54,8 @@ def run_pipeline(binary, g, factory, tmp, extra=None, flags=(), tag=None, iq=Non
         for sub in ("OUT", "dump"):
             shutil.rmtree(os.path.join(d, sub))
             os.makedirs(os.path.join(d, sub))
-        r = subprocess.run([binary, "-c", os.path.join(d, "cfg.json"), "-d", os.path.join(d, "dump"), "-r", "-q", *flags, wav],
+        r = subprocess.run([binary, "-c", os.path.join(d, "cfg.json"), "-d", os.path.join(d, "dump"),
+                            *(("-r",) if dump_rows else ()), "-q", *flags, wav],
                            cwd=d, capture_output=True, text=True)
         if r.returncode == 0:
             break
@@ -62,7 +63,8 @@ def run_pipeline(binary, g, factory, tmp, extra=None, flags=(), tag=None, iq=Non
         raise AssertionError("%s failed rc=%d: %s" % (binary, r.returncode, r.stderr[-2000:]))
     bins = g["meta"]["bins"]
     out = dict(
-        rows=np.fromfile(os.path.join(d, "dump", "rows.f32"), dtype=np.float32).reshape(-1, bins),
+        rows=(np.fromfile(os.path.join(d, "dump", "rows.f32"), dtype=np.float32).reshape(-1, bins)
+              if dump_rows else None),
         info=np.fromfile(os.path.join(d, "dump", "rowinfo.bin"), dtype=ROWINFO),
         npa=np.fromfile(os.path.join(d, "dump", "noise.bin"), dtype=NPA),
         bolid=open(os.path.join(d, "dump", "bolid.txt")).read(),
@@ -176,6 +178,65 @@ def _dropin_once(name, batch, narrow=False):
             n_checked += 1
         assert n_checked >= 2
         assert sorted(got["csv"]) == sorted(ref["csv"]) or len(got["csv"]) == len(ref["csv"])
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("narrow", [False, True])
+def test_long_run_that_laps_the_row_ring(narrow):
+    _retry_reference_races(_lapping_once, narrow)
+
+
+def _lapping_once(narrow):
+    """The recorders' worker threads read the row ring, the handle table and the raw ring after the
+    fact (reference src/WaterfallBackend.cpp:60-108); nothing in the reference stops the producer from
+    overwriting what a queued snapshot still needs.  300 s of station I/Q lap the golden configuration's
+    ring (752 rows = 32 s) nine times, and behind the CUDA backend the producer outruns the FITS
+    writers: without the adapter's back-pressure (CudaWaterfallBackend::waitForWriters) files come out
+    with rows, times and names of one ring capacity later.  Same files as the stock backend expected."""
+    if not (os.path.exists(REF_BIN) and os.path.exists(CUDA_BIN)):
+        pytest.fail("prebuilt binaries missing: run __graft_entry__.build() in the build container")
+    g = load_golden("c2b_16k")
+    sr = g["sample_rate"]
+    spec = synth.SynthSpec(sample_rate=sr, n_samples=300 * sr, seed=0x1A9, carrier_freq=26700.3,
+                           meteor_band=(26450.0, 26550.0))
+    iq = synth.generate_int16(spec)
+    tmp = tempfile.mkdtemp(prefix="ro_dropin_lap_")
+    try:
+        # no -r row dump for 7000 rows of 64 KB: rows are compared through the FITS files
+        ref = run_pipeline(REF_BIN, g, "waterfall", tmp, iq=iq, dump_rows=False)
+        for attempt in range(6):            # the reference's gmtime race, see _dropin_once
+            got = run_pipeline(CUDA_BIN, g, "waterfall_cuda", tmp, {"cuda_batch_frames": 64},
+                               flags=("-N",) if narrow else (), iq=iq, dump_rows=False)
+            if sorted(got["fits"]) == sorted(ref["fits"]):
+                break
+            shutil.rmtree(os.path.join(tmp, "waterfall_cuda"))
+        assert len(ref["info"]) > 8 * 752
+        for k in ("mark", "sec", "usec"):
+            assert np.array_equal(got["info"][k], ref["info"][k])
+        eb = [l.split(";") for l in ref["bolid"].strip().splitlines()]
+        gb = [l.split(";") for l in got["bolid"].strip().splitlines()]
+        assert len(eb) == len(gb) and len(eb) >= 10
+        for e, q in zip(eb, gb):
+            assert e[3:5] == q[3:5]
+        only_ref = sorted(set(ref["fits"]) - set(got["fits"]))
+        only_got = sorted(set(got["fits"]) - set(ref["fits"]))
+        assert not only_ref and not only_got, (len(ref["fits"]), only_ref[:5], only_got[:5])
+        peak = max(float(np.abs(v["data"]).max()) for fn, v in ref["fits"].items() if "raws" not in fn)
+        for fn in ref["fits"]:
+            a, b = ref["fits"][fn], got["fits"][fn]
+            assert a["shape"] == b["shape"], fn
+            assert a["cards"] == b["cards"], (fn, [x for x in zip(a["cards"], b["cards"]) if x[0] != x[1]])
+            if "raws" in fn:
+                assert np.array_equal(a["data"], b["data"]), fn
+            else:
+                # the full row's peak is not in the file: the largest pixel of any file of this run (the carrier
+                # is inside the recorded band) stands in for it
+                err = np.abs(a["data"].astype(np.float64) - b["data"])
+                assert (err <= np.maximum(REL_TOL * np.abs(a["data"]), FLOOR_PEAK * peak)).all(), fn
+        print("[dropin lap] %d rows, %d events, %d FITS files identical in name, header and raw I/Q"
+              % (len(ref["info"]), len(eb), len(ref["fits"])))
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
 
