@@ -397,6 +397,7 @@ class SnapshotDesc:
     time: WFTime              # fftMarkToTime(start) -> CRVAL2 / DATE-OBS
     global_start: int         # global row number of the first row (None-like -1 if unknown)
     raw: bool = False
+    written: bool = True      # set by run_recorders: did the worker thread get to write it (see there)
 
 
 def file_basename(t: WFTime, origin: str, typ: str, ext: str = "fits") -> str:
@@ -600,4 +601,12 @@ def run_recorders(rows_or_none, n_rows: int, times: Sequence[WFTime], recorders:
                 r.update(row)
     for r in recorders:
         r.stop()
+    # SnapshotRecorder::threadMethod (src/WaterfallBackend.cpp:60-104): a queued snapshot is written once
+    # buffer_->size(start) >= length and put back otherwise; after Channel::close the queue is drained one
+    # last time and what is still incomplete is dropped.  A bolid snapshot reaches `advance` rows past
+    # the last detection but is queued only `jitter` rows after it, so an event near the end of the
+    # stream is reported and never gets its file.
+    for r in recorders:
+        for d in r.out:
+            d.written = n_rows - d.global_start >= d.length
     return ring

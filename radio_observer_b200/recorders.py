@@ -109,13 +109,22 @@ def plan_snapshots(n_rows: int, times: Sequence[Tuple[int, int]], *, sample_rate
 
 
 def plan_bolids(events: Sequence[A.BolidEvent], times: Sequence[Tuple[int, int]], *, sample_rate: int, bins: int,
-                overlap: int, snapshot_length: float, origin: str, output_type: str = "blid") -> List[PlannedFile]:
+                overlap: int, snapshot_length: float, origin: str, output_type: str = "blid",
+                n_rows: Optional[int] = None) -> List[PlannedFile]:
     """BolidRecorder: one file per event, named at the first detection with the stamp of its start row,
-    length capped to snapshotRows when it is written (src/BolidRecorder.cpp:171-180, :112-116)."""
+    length capped to snapshotRows when it is written (src/BolidRecorder.cpp:171-180, :112-116).
+
+    An event is emitted `jitter` rows after its last detection, but its snapshot runs `advance` rows
+    past it: the worker thread keeps the snapshot back until those rows have arrived
+    (`buffer_->size(snapshot->start) >= snapshot->length`, src/WaterfallBackend.cpp:77) and drops it if
+    the stream ends first (the last pass after Channel::close, :66-104).  With `n_rows` (rows of the
+    whole stream) such events get no file, as in the reference; the event itself was still reported."""
     fsr = A.fft_sample_rate(sample_rate, bins, A.clamp_overlap(bins, overlap))
     S = snapshot_rows(snapshot_length, fsr)
     out = []
     for ev in events:
+        if n_rows is not None and n_rows - ev.start_row < min(S, ev.length):
+            continue
         t = _stamp(times, ev.start_row)
         out.append(PlannedFile(output_type, ev.start_row, min(S, ev.length), t,
                                F.file_basename(t[0], t[1], origin, output_type), ev))

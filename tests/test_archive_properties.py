@@ -81,6 +81,12 @@ def test_trigger_and_bolid_planning_equal_the_oracle_model(seed, n_rows, advance
         # the model's ring has not wrapped here, so its ring index is the global row
         if model.ring.pushed <= model.ring.capacity:
             assert pl.file_name == d.file_name.split("/")[-1] and pl.time == (d.time.sec, d.time.usec)
+    # files the reference's worker thread gets to write before the stream ends (see run_recorders)
+    if model.ring.pushed <= model.ring.capacity:
+        kept = P.plan_bolids(trig.events, ptimes, sample_rate=sr, bins=bins, overlap=ov, snapshot_length=3, origin="x",
+                             n_rows=n_rows)
+        assert [(pl.file_name, pl.length) for pl in kept] == \
+            [(d.file_name.split("/")[-1], d.length) for d in model.out if d.written]
 
 
 @settings(max_examples=80, deadline=None)

@@ -84,3 +84,70 @@ def test_planned_files_match_what_the_reference_wrote(name, tmp_path):
         assert hashlib.sha256(np.ascontiguousarray(data).tobytes()).hexdigest() == want["sha256"]
         n_px += 1
     assert n_px >= 1
+
+
+def test_event_cut_short_by_the_end_of_the_stream_gets_no_file(tmp_path):
+    """A bolid snapshot reaches `advance` rows past the last detection but is queued `jitter` rows after
+    it; the reference's worker thread holds it back until the rows are there and drops it when the stream
+    ends first (src/WaterfallBackend.cpp:60-104).  200 s of the bench's station recording end inside such
+    an event: the stock Pipeline (oracle/_ref, the checker) reports 34 events and writes 33 bolid files.
+    The oracle's model and the archive path's planner must both leave that file out."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    import bench
+    from radio_observer_b200 import synth
+    if not os.path.exists(bench.REF_BIN):
+        pytest.fail("oracle/_ref/ref_oracle missing: run __graft_entry__.build() in the build container")
+    sr, bins, ov = bench.SR, bench.BINS, bench.OVERLAP
+    n = 200 * sr
+    wav = str(tmp_path / "in.wav")
+    synth.write_wav(wav, bench.host_station_iq(n, 0x5EED0002), sr)
+    out, dump = tmp_path / "out", tmp_path / "dump"
+    cfg = tmp_path / "cfg.json"
+    cfg.write_text(bench.ref_config_json(str(out), "waterfall", None))
+    for attempt in range(50):              # the reference's start-up race, see test_dropin_adapter.run_pipeline
+        for d in (out, dump):
+            if d.exists():
+                import shutil
+                shutil.rmtree(d)
+            d.mkdir()
+        rc = subprocess.call([bench.REF_BIN, "-c", str(cfg), "-d", str(dump), "-q", wav], cwd=str(tmp_path),
+                             stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        if rc == 0 and os.listdir(out):
+            break
+    else:
+        raise AssertionError("reference run failed")
+    wrote = sorted(f for f in os.listdir(out) if f.endswith("_blid.fits"))
+    reported = (dump / "bolid.txt").read_text().count("\n")
+    assert reported == len(wrote) + 1 >= 10
+    npa = np.fromfile(str(dump / "noise.bin"), dtype=np.dtype([("noise", "<f4"), ("peakfreq", "<f4"), ("mag", "<f4")]))
+    n_rows = len(npa)
+    assert n_rows == A.frame_count(n, bins, ov)
+    keys = dict(low_detect_freq=26450.0, hi_detect_freq=26550.0, low_noise_freq=26000.0, hi_noise_freq=26300.0,
+                avg_freq_range=40.0, advance_time=5.0, jitter_time=2.0)
+    b = A.bolid_bands(sr, bins, ov, **keys)
+    peaks = np.array([R.frequency_to_bin(f, sr, bins) - b["det_lo"] for f in npa["peakfreq"]], dtype=np.int32)
+    # the checker's model
+    model = R.BolidModel(sample_rate=sr, bins=bins, overlap=ov, origin="bench", output_type="blid", snapshot_length=60,
+                         low_freq=26200.0, hi_freq=26800.0, **keys)
+    R.run_recorders(None, n_rows, R.frame_times(n, bins, ov, sr, block=1024), [model], bins,
+                    npa=(npa["noise"], peaks, npa["mag"]))
+    assert len(model.events) == reported
+    assert sorted(d.file_name.split("/")[-1] for d in model.out if d.written) == wrote
+    assert [d.written for d in model.out].count(False) == 1 and not model.out[-1].written
+    # the archive path's planner
+    recs = np.zeros(n_rows, dtype=DET_DTYPE)
+    recs["noise"], recs["peak"], recs["avg"] = npa["noise"], peaks, npa["mag"]
+    trig = A.BolidTrigger(det_lo=b["det_lo"], advance=b["advance"], jitter=b["jitter"], fft_sample_rate=A.fft_sample_rate(sr, bins, ov))
+    trig.feed(recs)
+    assert len(trig.events) == reported
+    times = P.frame_times(n_rows, bins, ov, sr, block=1024)
+    common = dict(sample_rate=sr, bins=bins, overlap=ov, snapshot_length=60, origin="bench")
+    assert sorted(p.file_name for p in P.plan_bolids(trig.events, times, n_rows=n_rows, **common)) == wrote
+    assert len(P.plan_bolids(trig.events, times, **common)) == reported
+    # the snapshot recorder of the same run
+    snaps = P.plan_snapshots(n_rows, times, sample_rate=sr, bins=bins, overlap=ov, snapshot_length=60, origin="bench")
+    assert sorted(p.file_name for p in snaps) == sorted(f for f in os.listdir(out) if f.endswith("_snap.fits"))

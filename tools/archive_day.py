@@ -98,7 +98,7 @@ def main():
             times = P.frame_times(int(F), BINS, OVERLAP, SR, block=1024)
             common = dict(sample_rate=SR, bins=BINS, overlap=OVERLAP, origin="archive")
             snaps = P.plan_snapshots(int(F), times, snapshot_length=60, **common)
-            blids = [p for p in P.plan_bolids(trig.events, times, snapshot_length=60, **common) if p.start_row >= 0]
+            blids = [p for p in P.plan_bolids(trig.events, times, snapshot_length=60, n_rows=int(F), **common) if p.start_row >= 0]
             with open(os.path.join(a.out, "archive_meta.csv"), "w") as csv:
                 csv.write("# file name; noise; peak f.; mag.; duration\n")
                 for p in blids:

@@ -106,6 +106,43 @@ def main():
                 print(json.dumps(rec), flush=True)
                 out.append(rec)
                 shutil.rmtree(d, ignore_errors=True)
+        # The archive path on the same samples (radio_observer_b200/archive.py + recorders.py: whole-array
+        # C-ABI call, trigger state machine and file planning in Python): which snapshot and bolid files it
+        # would write, and its events, against what the stock Pipeline wrote.
+        if ref is not None:
+            from radio_observer_b200 import archive as A, recorders as P
+            iq = synth.read_wav(wav)[0] if hasattr(synth, "read_wav") else bench.host_station_iq(n, 0x5EED0002)
+            keys = dict(low_detect_freq=26450.0, hi_detect_freq=26550.0, low_noise_freq=26000.0, hi_noise_freq=26300.0,
+                        avg_freq_range=40.0, advance_time=5.0, jitter_time=2.0)
+            b = A.bolid_bands(bench.SR, bench.BINS, bench.OVERLAP, **keys)
+            band = (A.frequency_to_bin(26200.0, bench.SR, bench.BINS), A.frequency_to_bin(26800.0, bench.SR, bench.BINS))
+            t0 = time.perf_counter()
+            rows, det, _ = A.reprocess_archive(iq, bench.BINS, bench.OVERLAP, sample_rate=bench.SR, bands=[band], detector=b)
+            trig = A.BolidTrigger(det_lo=b["det_lo"], advance=b["advance"], jitter=b["jitter"],
+                                  fft_sample_rate=A.fft_sample_rate(bench.SR, bench.BINS, bench.OVERLAP))
+            trig.feed(det)
+            F = len(rows)
+            times = P.frame_times(int(F), bench.BINS, bench.OVERLAP, bench.SR, block=1024)
+            common = dict(sample_rate=bench.SR, bins=bench.BINS, overlap=bench.OVERLAP, origin="bench")
+            snaps = P.plan_snapshots(int(F), times, snapshot_length=60, **common)
+            blids = P.plan_bolids(trig.events, times, snapshot_length=60, n_rows=int(F), **common)
+            dt = time.perf_counter() - t0
+            mine = set(p.file_name for p in snaps + blids)
+            theirs = set(x for x in ref["names"] if x.endswith("_snap.fits") or x.endswith("_blid.fits"))
+            ev_same = len(trig.events) == ref["bolid"].count("\n")
+            for ev, line in zip(trig.events, ref["bolid"].strip().splitlines()):
+                f = A.event_fields(ev, sample_rate=bench.SR, bins=bench.BINS, overlap=bench.OVERLAP,
+                                   low_detect_freq=keys["low_detect_freq"], hi_detect_freq=keys["hi_detect_freq"])
+                x = line.split(";")
+                if ("%.9g" % f["peak_freq"], "%.9g" % f["min_freq"], "%.9g" % f["max_freq"], "%d" % f["end_sample"]) != \
+                        (x[1], x[3], x[4], x[6]):
+                    ev_same = False
+            rec = {"variant": "archive_path", "wall_s": round(dt, 3), "msamples_s": round(n / dt / 1e6, 1), "rows": int(F),
+                   "against_stock": {"events": len(trig.events), "event_freq_band_span_identical": ev_same,
+                                     "snap_blid_files": len(mine), "n_only_stock": len(theirs - mine),
+                                     "n_only_here": len(mine - theirs),
+                                     "names_only_stock": sorted(theirs - mine)[:6], "names_only_here": sorted(mine - theirs)[:6]}}
+            print(json.dumps(rec), flush=True)
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
     return 0
