@@ -356,7 +356,8 @@ int launch_fft(ro_wf *h, cudaStream_t s, const void *d_iq, float *d_rows, long l
 		}
 		return RO_OK;
 	}
-	if (h->fused_ok && ((uintptr_t)d_rows & 15) == 0 && (row_stride & 3) == 0) {
+	if (h->fused_ok && ((uintptr_t)d_rows & 15) == 0 && (row_stride & 3) == 0 &&
+	    (h->fmt != ro::FMT_FLOAT32 || ((uintptr_t)d_iq & 7) == 0)) {
 		const long long cap = h->v2f_grid_cap;
 		const long long fpc = (n_frames + cap - 1) / cap;          // contiguous frames per CTA
 		const int grid = (int)((n_frames + fpc - 1) / fpc);
@@ -731,9 +732,9 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 		}
 	}
 	h->fused_ok = false;
-	if (h->split_ok && log2nb == 14 && (h->log2na == 1 || h->log2na == 2) && h->fmt == ro::FMT_INT16 &&
-	    !getenv("RO_NO_FUSED") &&
-	    ro::v2_pick(14, h->log2na == 1 ? ro::V2_FUSED1 : ro::V2_FUSED2, false, &h->v2f)) {
+	if (h->split_ok && log2nb == 14 && (h->log2na == 1 || h->log2na == 2) && !getenv("RO_NO_FUSED") &&
+	    (h->fmt == ro::FMT_INT16 ? ro::v2_pick(14, h->log2na == 1 ? ro::V2_FUSED1 : ro::V2_FUSED2, false, &h->v2f)
+	     : h->fmt == ro::FMT_FLOAT32 && h->log2na == 1 && !getenv("RO_NO_FUSED_F32") && ro::v2_pick_fused_f32(&h->v2f))) {
 		CUH(cudaFuncSetAttribute(h->v2f.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->v2f.smem));
 		int occ4 = 0;
 		CUH(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, h->v2f.fn, h->v2f.threads, h->v2f.smem));

@@ -54,8 +54,11 @@ enum { MODE_DIRECT = 0,   // int16 I/Q read from global memory, row = item
                           // radix-Na step done): item = frame*Na + r, output k is bin Na*k + r
        MODE_FUSED1 = 3,   // like MODE_SPLIT with Na = 2, 4, but the radix-Na step is done here, per frame,
        MODE_FUSED2 = 4,   // by the thread that needs its results: no scratch round trip through HBM
-       MODE_DIRECT_F32 = 5 }; // MODE_DIRECT for float32 I/Q (the reference's raw-TCP / JACK encoding)
-constexpr bool mode_is_split(int m) { return m == MODE_SPLIT || m == MODE_FUSED1 || m == MODE_FUSED2; }
+       MODE_DIRECT_F32 = 5,   // MODE_DIRECT for float32 I/Q (the reference's raw-TCP / JACK encoding)
+       MODE_FUSED1_F32 = 6 }; // MODE_FUSED1 for float32 I/Q
+constexpr bool mode_is_split(int m) { return m == MODE_SPLIT || m == MODE_FUSED1 || m == MODE_FUSED2 || m == MODE_FUSED1_F32; }
+template <bool F32IN> struct raw_word { typedef unsigned int type; };          // one int16 I/Q pair
+template <> struct raw_word<true> { typedef unsigned long long type; };       // one float32 I/Q pair
 
 __device__ __forceinline__ unsigned int smem_u32(const void *p)
 {
@@ -129,6 +132,10 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned in
 	             :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// one raw I/Q pair -> packed complex float
+__device__ __forceinline__ c64 raw_to_c64(unsigned int w) { return short2_to_c64(w); }
+__device__ __forceinline__ c64 raw_to_c64(unsigned long long w) { return w; }
+
 // bytes of dynamic shared memory the kernel needs
 template <int LOG2N, int P, int R3, int MODE>
 constexpr size_t wf2_smem_bytes()
@@ -150,9 +157,10 @@ wf_fft2_kernel(const Wf2Params p)
 #ifndef RO_L2_PREFETCH
 #define RO_L2_PREFETCH 1
 #endif
-	constexpr bool FUSED = MODE == MODE_FUSED1 || MODE == MODE_FUSED2;
+	constexpr bool FIN32 = MODE == MODE_FUSED1_F32;           // fused, float32 input
+	constexpr bool FUSED = MODE == MODE_FUSED1 || MODE == MODE_FUSED2 || FIN32;
 	constexpr bool F32 = MODE == MODE_DIRECT_F32;
-	constexpr int FLA = FUSED ? MODE - MODE_FUSED1 + 1 : 0;   // log2(Na) of the fused modes
+	constexpr int FLA = FIN32 ? 1 : FUSED ? MODE - MODE_FUSED1 + 1 : 0;   // log2(Na) of the fused modes
 	constexpr bool SPLIT = MODE == MODE_SPLIT || FUSED;
 #ifndef RO_FUSED_DIT
 #define RO_FUSED_DIT 1
@@ -269,7 +277,8 @@ wf_fft2_kernel(const Wf2Params p)
 			const int r = (int)(f & (NA - 1));
 			unsigned long long *scr = p.scratch + (size_t)blockIdx.x * (NA - 1) * N;
 			if (r == 0) {
-				const unsigned int *src = reinterpret_cast<const unsigned int *>(p.raw) + (f >> FLA) * hop;
+				typedef typename raw_word<FIN32>::type raw_t;
+				const raw_t *src = reinterpret_cast<const raw_t *>(p.raw) + (f >> FLA) * hop;
 				const unsigned long long *twb = reinterpret_cast<const unsigned long long *>(p.tw_big);
 				// loads in bursts of CH positions m, fenced from the arithmetic and the stores: one memory
 				// latency per burst instead of one per position (ptxas will not move loads above the stores)
@@ -281,10 +290,10 @@ wf_fft2_kernel(const Wf2Params p)
 #ifndef RO_FUSED_CH
 #define RO_FUSED_CH 16
 #endif
-				constexpr int CH = RO_FUSED_CH / NA;
+				constexpr int CH = RO_FUSED_CH / NA / (FIN32 ? 2 : 1);      // float32: twice the registers per sample in flight
 #pragma unroll
 				for (int c0 = 0; c0 < R1; c0 += CH) {
-					unsigned int raw[CH][NA];
+					raw_t raw[CH][NA];
 					float wv[CH][NA];
 					c64 bb[CH][FLA];
 					ptxas_fence(p.stagger & 1);
@@ -308,7 +317,7 @@ wf_fft2_kernel(const Wf2Params p)
 						c64 xq[NA];
 #pragma unroll
 						for (int q = 0; q < NA; q++)
-							xq[q] = mul2(add2(short2_to_c64(raw[j][q]), gain2), pk(wv[j][q], wv[j][q]));
+							xq[q] = mul2(add2(raw_to_c64(raw[j][q]), gain2), pk(wv[j][q], wv[j][q]));
 						fft_dif2<NA>(xq);
 						if (TWC) xq[1] = cmul2(cmul2(xq[1], wt), cw64((c0 + j) & 31), -sw64((c0 + j) & 31));
 						else twiddle_powers2<NA>(xq, bb[j]);
@@ -320,7 +329,7 @@ wf_fft2_kernel(const Wf2Params p)
 #if RO_L2_PREFETCH
 				if (f + NA < f1) {     // the hop new samples of the next frame
 					const unsigned char *nx = reinterpret_cast<const unsigned char *>(src + NBIG);
-					for (long long o = (long long)t * 128; o < 4 * hop; o += (long long)T * 128)
+					for (long long o = (long long)t * 128; o < (long long)sizeof(raw_t) * hop; o += (long long)T * 128)
 						asm volatile("prefetch.global.L2 [%0];" :: "l"(nx + o));
 				}
 #endif

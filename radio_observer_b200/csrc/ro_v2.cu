@@ -115,7 +115,7 @@ cudaError_t v2_launch_fused(const V2Kernel &k, int grid, cudaStream_t s, const v
                             long long row_stride, long long n_frames, long long hop, long long frames_per_cta,
                             float iq_gain, int pair, int stagger)
 {
-	const int la = k.mode - V2_FUSED1 + 1;
+	const int la = k.mode == V2_FUSED1_F32 ? 1 : k.mode - V2_FUSED1 + 1;
 	Wf2Params p;
 	p.iq = NULL;
 	p.window_half = NULL;

@@ -5,7 +5,7 @@
 
 namespace ro {
 
-enum { V2_DIRECT = 0, V2_STAGED = 1, V2_SPLIT = 2, V2_FUSED1 = 3, V2_FUSED2 = 4, V2_DIRECT_F32 = 5 };   // = MODE_* of ro_kernels2.cuh
+enum { V2_DIRECT = 0, V2_STAGED = 1, V2_SPLIT = 2, V2_FUSED1 = 3, V2_FUSED2 = 4, V2_DIRECT_F32 = 5, V2_FUSED1_F32 = 6 };   // = MODE_* of ro_kernels2.cuh
 
 struct V2Kernel {
 	const void *fn;      // kernel symbol (for attribute / occupancy queries)
@@ -22,6 +22,8 @@ bool v2_pick(int log2n, int mode, bool gain, V2Kernel *out);
 
 // The same for float32 I/Q input (N = 1024 .. 16384), launched with v2_launch like V2_DIRECT (ro_v2f.cu).
 bool v2_pick_f32(int log2n, bool gain, V2Kernel *out);
+// V2_FUSED1 for float32 I/Q (frames of 2*16384 points), launched with v2_launch_fused; d_raw 8-byte aligned.
+bool v2_pick_fused_f32(V2Kernel *out);
 
 // Launches it: n_frames items of `hop`-spaced N-sample windows of d_iq (int16 I/Q), or, for
 // V2_SPLIT, n_frames = frames*Na items of N packed complex floats each (d_iq = the scratch

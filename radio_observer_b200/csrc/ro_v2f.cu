@@ -34,4 +34,15 @@ bool v2_pick_f32(int log2n, bool gain, V2Kernel *out)
 	}
 }
 
+bool v2_pick_fused_f32(V2Kernel *out)
+{
+	out->log2n = 14;
+	out->mode = V2_FUSED1_F32;
+	out->gain = false;                           // the gain is a kernel parameter here
+	out->threads = (1 << 14) / 32;
+	out->smem = wf2_smem_bytes<14, 32, 16, MODE_FUSED1_F32>();
+	out->fn = (const void *)wf_fft2_kernel<14, 32, 16, MODE_FUSED1_F32, false, 1>;
+	return true;
+}
+
 }  // namespace ro

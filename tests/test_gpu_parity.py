@@ -81,6 +81,32 @@ def test_rows_match_oracle_float32_and_gain(bins, overlap):
     wf.close()
 
 
+@pytest.mark.parametrize("overlap,iq_gain", [(24576, 0.125), (16384, 0.0), (3, 0.0)])
+def test_float32_32k_fused_many_frames_per_cta(overlap, iq_gain, monkeypatch):
+    """float32 frames of 32768 points run in ONE kernel (MODE_FUSED1_F32: radix-2 step + two 16k
+    transforms per frame).  400 frames make every CTA of the persistent grid walk several frames
+    (its private scratch slice is rewritten per frame); the same input through the split path
+    (RO_NO_FUSED_F32=1) is the second witness."""
+    bins = 32768
+    n_frames = 400 if overlap else 60
+    n = bins + (n_frames - 1) * (bins - overlap) + 5
+    spec = synth.SynthSpec(sample_rate=96000, n_samples=n, seed=11 + overlap, carrier_freq=21999.7)
+    iq = synth.generate_float32(spec)
+    wf = ro.Waterfall(bins, overlap, sample_rate=96000, in_format=ro.IN_FLOAT32, iq_gain=iq_gain)
+    rows, _, nf = wf.process_host(iq)
+    wf.close()
+    ref = R.waterfall_rows(iq, bins, overlap, iq_gain=iq_gain)
+    assert nf == len(ref) == n_frames
+    assert_rows_close(rows, ref, f"float32 fused N=32768 ov={overlap}")
+    monkeypatch.setenv("RO_NO_FUSED_F32", "1")
+    wf2 = ro.Waterfall(bins, overlap, sample_rate=96000, in_format=ro.IN_FLOAT32, iq_gain=iq_gain)
+    rows2, _, nf2 = wf2.process_host(iq)
+    wf2.close()
+    assert nf2 == nf
+    assert_rows_close(rows2, ref, "float32 split N=32768")
+    assert_rows_close(rows, rows2.astype(np.float64), "fused against split")
+
+
 def test_complex64_input_is_narrowed_like_float32():
     bins, overlap = 4096, 3072
     spec = synth.SynthSpec(sample_rate=48000, n_samples=bins * 4, seed=3)
