@@ -290,7 +290,10 @@ wf_fft2_kernel(const Wf2Params p)
 #ifndef RO_FUSED_CH
 #define RO_FUSED_CH 16
 #endif
-				constexpr int CH = RO_FUSED_CH / NA / (FIN32 ? 2 : 1);      // float32: twice the registers per sample in flight
+#ifndef RO_FUSED_CH_F32
+#define RO_FUSED_CH_F32 16
+#endif
+				constexpr int CH = (FIN32 ? RO_FUSED_CH_F32 : RO_FUSED_CH) / NA;   // float32: twice the registers per sample in flight
 #pragma unroll
 				for (int c0 = 0; c0 < R1; c0 += CH) {
 					raw_t raw[CH][NA];
