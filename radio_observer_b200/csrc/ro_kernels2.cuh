@@ -541,8 +541,15 @@ wf_fft2_kernel(const Wf2Params p)
 							for (int c = 0; c < G; c++) ev[c] = stash[(k3 * G + c) * T + t];
 							const int k = k3 * (N / R3) + G * t;
 							if (G == 2 && la == 1) {
-								*reinterpret_cast<float4 *>(row + (((k << 1) + big_half) & big_mask)) =
-									make_float4(ev[0], mag[k3][0], ev[1], mag[k3][1]);
+								// float32 fused 32k (-DRO_ROWS_STCS=1): evict-first stores, so that the rows do not
+								// push the overlapped input (re-read by the next frame) out of L2
+#ifndef RO_ROWS_STCS
+#define RO_ROWS_STCS 0
+#endif
+								float4 *dst = reinterpret_cast<float4 *>(row + (((k << 1) + big_half) & big_mask));
+								const float4 val = make_float4(ev[0], mag[k3][0], ev[1], mag[k3][1]);
+								if (FIN32 && RO_ROWS_STCS) __stcs(dst, val);
+								else *dst = val;
 							} else {
 #pragma unroll
 								for (int c = 0; c < G; c++)
