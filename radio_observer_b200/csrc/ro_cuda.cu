@@ -356,8 +356,9 @@ int launch_fft(ro_wf *h, cudaStream_t s, const void *d_iq, float *d_rows, long l
 		}
 		return RO_OK;
 	}
+	// the fused long-frame kernel stages samples with cp.async.bulk: 16-byte aligned frame starts
 	if (h->fused_ok && ((uintptr_t)d_rows & 15) == 0 && (row_stride & 3) == 0 &&
-	    (h->fmt != ro::FMT_FLOAT32 || ((uintptr_t)d_iq & 7) == 0)) {
+	    ((uintptr_t)d_iq & 15) == 0 && ((long long)h->hop * h->in_bytes) % 16 == 0) {
 		const long long cap = h->v2f_grid_cap;
 		const long long fpc = (n_frames + cap - 1) / cap;          // contiguous frames per CTA
 		const int grid = (int)((n_frames + fpc - 1) / fpc);
@@ -641,9 +642,9 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 	CUH(cudaMalloc(&h->d_tw, sizeof(float2) * N));
 	CUH(cudaMemcpy(h->d_window, win.data(), sizeof(float) * N, cudaMemcpyHostToDevice));
 	CUH(cudaMemcpy(h->d_tw, tw.data(), sizeof(float2) * N, cudaMemcpyHostToDevice));
-	{   // v2 eligibility: int16 input, an instantiated size, and w[i] == w[N-1-i] bit for bit
-		bool sym = true;
-		for (int i = 0; i < N / 2 && sym; i++) sym = memcmp(&win[i], &win[N - 1 - i], sizeof(float)) == 0;
+	bool sym = true;                          // w[i] == w[N-1-i] bit for bit
+	for (int i = 0; i < N / 2 && sym; i++) sym = memcmp(&win[i], &win[N - 1 - i], sizeof(float)) == 0;
+	{   // v2 eligibility: an instantiated size and a symmetric window
 		const bool gain = cfg->iq_gain != 0.0;
 		h->v2_ok = false;
 		const char *force_v1 = getenv("RO_FORCE_V1");
@@ -732,9 +733,9 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 		}
 	}
 	h->fused_ok = false;
-	if (h->split_ok && log2nb == 14 && (h->log2na == 1 || h->log2na == 2) && !getenv("RO_NO_FUSED") &&
-	    (h->fmt == ro::FMT_INT16 ? ro::v2_pick(14, h->log2na == 1 ? ro::V2_FUSED1 : ro::V2_FUSED2, false, &h->v2f)
-	     : h->fmt == ro::FMT_FLOAT32 && h->log2na == 1 && !getenv("RO_NO_FUSED_F32") && ro::v2_pick_fused_f32(&h->v2f))) {
+	if (h->split_ok && sym && log2nb == 14 && h->log2na == 1 && !getenv("RO_NO_FUSED") &&
+	    (h->fmt == ro::FMT_INT16 ? ro::v2_pick(14, ro::V2_FUSED1, false, &h->v2f)
+	     : h->fmt == ro::FMT_FLOAT32 && !getenv("RO_NO_FUSED_F32") && ro::v2_pick_fused_f32(&h->v2f))) {
 		CUH(cudaFuncSetAttribute(h->v2f.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->v2f.smem));
 		int occ4 = 0;
 		CUH(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, h->v2f.fn, h->v2f.threads, h->v2f.smem));

@@ -52,11 +52,15 @@ enum { MODE_DIRECT = 0,   // int16 I/Q read from global memory, row = item
        MODE_STAGED = 1,   // int16 I/Q through the TMA-staged shared-memory ring, row = item
        MODE_SPLIT  = 2,   // packed complex float from wf_split_kernel (already windowed, first
                           // radix-Na step done): item = frame*Na + r, output k is bin Na*k + r
-       MODE_FUSED1 = 3,   // like MODE_SPLIT with Na = 2, 4, but the radix-Na step is done here, per frame,
-       MODE_FUSED2 = 4,   // by the thread that needs its results: no scratch round trip through HBM
+       MODE_FUSED1 = 3,   // like MODE_SPLIT with Na = 2, but the radix-2 step is done here, per frame, by the
+                          // thread that needs its results: no scratch round trip through HBM
        MODE_DIRECT_F32 = 5,   // MODE_DIRECT for float32 I/Q (the reference's raw-TCP / JACK encoding)
        MODE_FUSED1_F32 = 6 }; // MODE_FUSED1 for float32 I/Q
-constexpr bool mode_is_split(int m) { return m == MODE_SPLIT || m == MODE_FUSED1 || m == MODE_FUSED2 || m == MODE_FUSED1_F32; }
+__host__ __device__ constexpr bool mode_is_fused(int m) { return m == MODE_FUSED1 || m == MODE_FUSED1_F32; }
+__host__ __device__ constexpr bool mode_is_split(int m) { return m == MODE_SPLIT || mode_is_fused(m); }
+__host__ __device__ constexpr bool mode_is_f32(int m) { return m == MODE_DIRECT_F32 || m == MODE_FUSED1_F32; }
+// MODE_FUSED*: bytes of the raw-sample / window staging ring beside the 64 KB stash, and of its barriers
+constexpr size_t FUSED_RING_BYTES = 32768, FUSED_BAR_BYTES = 512;
 template <bool F32IN> struct raw_word { typedef unsigned int type; };          // one int16 I/Q pair
 template <> struct raw_word<true> { typedef unsigned long long type; };       // one float32 I/Q pair
 
@@ -87,6 +91,16 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned int 
 		"bra WAIT_%=;\n\t"
 		"DONE_%=:\n\t}"
 		:: "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ bool mbar_test(unsigned long long *bar, unsigned int parity)
+{
+	unsigned int ok;
+	asm volatile(
+		"{\n\t.reg .pred p;\n\t"
+		"mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+		"selp.u32 %0, 1, 0, p;\n\t}"
+		: "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+	return ok != 0;
 }
 // Warps w, w+4, w+8, ... share one of the SM's four schedulers.  Left alone they issue their
 // shared-memory load bursts in lock step, receive their data together, then fight for the FMA
@@ -143,7 +157,8 @@ constexpr size_t wf2_smem_bytes()
 	constexpr size_t N = (size_t)1 << LOG2N;
 	constexpr size_t PAD1 = (R3 < 16) ? R3 : 0;
 	return sizeof(c64) * (N + P * PAD1) + (mode_is_split(MODE) ? 0 : sizeof(float) * (N / 2)) + 32 +
-	       (MODE == MODE_STAGED ? 4 * N : 0) + (mode_is_split(MODE) && P / R3 >= 2 ? 4 * N : 0);
+	       (MODE == MODE_STAGED ? 4 * N : 0) + (mode_is_split(MODE) && P / R3 >= 2 ? 4 * N : 0) +
+	       (mode_is_fused(MODE) ? FUSED_RING_BYTES + FUSED_BAR_BYTES : 0);
 }
 
 template <int LOG2N, int P, int R3, int MODE, bool GAIN, int MINB>
@@ -157,10 +172,10 @@ wf_fft2_kernel(const Wf2Params p)
 #ifndef RO_L2_PREFETCH
 #define RO_L2_PREFETCH 1
 #endif
-	constexpr bool FIN32 = MODE == MODE_FUSED1_F32;           // fused, float32 input
-	constexpr bool FUSED = MODE == MODE_FUSED1 || MODE == MODE_FUSED2 || FIN32;
+	constexpr bool FIN32 = MODE == MODE_FUSED1_F32;   // fused, float32 input
+	constexpr bool FUSED = mode_is_fused(MODE);
 	constexpr bool F32 = MODE == MODE_DIRECT_F32;
-	constexpr int FLA = FIN32 ? 1 : FUSED ? MODE - MODE_FUSED1 + 1 : 0;   // log2(Na) of the fused modes
+	constexpr int FLA = FUSED ? 1 : 0;   // log2(Na) of the fused modes
 	constexpr bool SPLIT = MODE == MODE_SPLIT || FUSED;
 #ifndef RO_FUSED_DIT
 #define RO_FUSED_DIT 1
@@ -180,15 +195,6 @@ wf_fft2_kernel(const Wf2Params p)
 	constexpr int SW = 16 / R3;
 	constexpr int NMASK = N - 1;
 	constexpr unsigned int CHUNK = 16384;      // bytes per bulk copy
-	// Pass 2 writes its outputs back into the row of S it read (see pass 2): 32*32*16 only.
-	// Correct (parity tests pass) but measured SLOWER on B200, 25.7 against 27.1 M frames/s: without
-	// the wait the early warps' store bursts collide with the load bursts of the chained late warps.
-	// Off; kept for A/B measurements (-DRO_INPLACE=1).
-#ifndef RO_INPLACE
-#define RO_INPLACE 0
-#endif
-	constexpr bool INPLACE = RO_INPLACE && R3 == 16 && P == 32;
-
 	extern __shared__ __align__(128) unsigned char smem_raw[];
 	c64 *S = reinterpret_cast<c64 *>(smem_raw);
 	float *win = reinterpret_cast<float *>(S + N + P * PAD1);
@@ -239,6 +245,72 @@ wf_fft2_kernel(const Wf2Params p)
 	}
 	const c64 gain2 = pk(0.f, p.iq_gain);
 
+	// ---- MODE_FUSED1*: the load phase of a 2N-point frame, staged by TMA ----
+	// A frame of 2N points needs, for every position m = n1*M + t of this thread, the samples and window
+	// values at m and N + m.  Round 1 fetched them with 4*R1 LDG per thread and frame and stalled on them
+	// (long_scoreboard 44 % of the stall samples).  Measured since (B200, round 2): with every load of the
+	// frame served by L2 the kernel sits on the L2 -> SM throughput, about 4.9 TB/s over the chip,
+	// whatever instruction fetches the bytes: LDG and cp.async.bulk give the same 7.6 M frames/s for the
+	// 640 KB a frame moved (samples 128, window 128, parked class 128 out + 128 back, row 128).  So the
+	// bytes had to go: the Nuttall table is symmetric (checked on the host), w[N + m] = w[N - 1 - m],
+	// and a burst that takes positions from BOTH ends of the range needs each window run once:
+	// burst b = positions b*HP .. b*HP + HP-1 and R1 - (b+1)*HP .. R1 - b*HP - 1; its stage holds four
+	// sample runs (q = 0, 1 x low, high) and two window runs (low, high), six cp.async.bulk copies that
+	// complete on the stage's `full` mbarrier.  Every warp reads its 32 columns with LDS (the q = 1 window
+	// value of a low position is element M-1-t of the mirrored segment in the high run, and vice versa)
+	// and releases the stage on its `empty` mbarrier (one arrival per warp).  The ring has three stages:
+	// stage 0 is memory of its own, stages 1 and 2 live in the 64 KB magnitude stash, which is idle
+	// during the load phase (written in pass 3 of the even class, read in pass 3 of the odd class; the
+	// last readers of a frame arrive on `stashfree`).  Burst b uses stage b % 3.  Schedule, no shared
+	// producer state: burst 0 of the next frame is issued right after this frame's load phase (a whole
+	// frame ahead), bursts 1 and 2 at the start of the load phase, burst b + 2 when warp b % 16 starts
+	// burst b; the empty-barrier parity to wait for is the complement of the consumer's own phase bit of
+	// that stage (its last use has been consumed).
+	static_assert(!FUSED || FLA == 1, "the fused kernel does the radix-2 step only");
+	constexpr int FNA = 1 << FLA;
+	constexpr int RAWB = FIN32 ? 8 : 4;
+	constexpr int HP = FIN32 ? 1 : 2;                              // positions per burst from each end
+	constexpr unsigned int RUN_RAW = (unsigned int)(HP * M) * RAWB, RUN_WIN = (unsigned int)(HP * M) * 4u;
+	constexpr unsigned int SB = 4u * RUN_RAW + 2u * RUN_WIN;       // bytes per stage: 24 KB (int16), 20 KB (float32)
+	constexpr int NST = 3;
+	constexpr int NB = R1 / (2 * HP);                              // bursts per frame
+	static_assert(!FUSED || (SB <= FUSED_RING_BYTES && 2 * SB <= 4u * N), "ring");
+	unsigned char *stash8 = reinterpret_cast<unsigned char *>(mbar + 4);
+	unsigned char *ded8 = stash8 + 4 * N;
+	unsigned long long *fullb = reinterpret_cast<unsigned long long *>(ded8 + FUSED_RING_BYTES);
+	unsigned long long *emptyb = fullb + NST, *stashfree = emptyb + NST;
+	unsigned int fullph = 0, stashph = 1;       // a fresh barrier passes a wait on parity 1
+	auto stage_ptr = [&](int s) -> unsigned char * { return s == 0 ? ded8 : stash8 + (s - 1) * SB; };
+	// all lanes of one warp: fill the stage of burst b of (batch-relative) frame fr
+	auto issue_burst = [&](long long fr, int b) {
+		if constexpr (FUSED) {
+			const int lane = t & 31;
+			const int s = b % 3;
+			mbar_wait(emptyb + s, ((fullph >> s) & 1u) ^ 1u);
+			if (lane == 0) mbar_expect_tx(fullb + s, SB);
+			__syncwarp();
+			if (lane < 6) {
+				const int pos0 = (lane & 1) ? R1 - (b + 1) * HP : b * HP;      // odd lanes: the high end
+				unsigned char *dst = stage_ptr(s);
+				if (lane < 4)      // sample run q = lane / 2
+					bulk_g2s(dst + lane * RUN_RAW,
+					         reinterpret_cast<const unsigned char *>(p.raw) + (fr * hop + (long long)(lane >> 1) * N + pos0 * M) * RAWB,
+					         RUN_RAW, fullb + s);
+				else               // window run of the first half of the table
+					bulk_g2s(dst + 4 * RUN_RAW + (lane & 1) * RUN_WIN, p.window_full + pos0 * M, RUN_WIN, fullb + s);
+			}
+			__syncwarp();
+		}
+	};
+	if constexpr (FUSED) {
+		if (t == 0) {
+			for (int s = 0; s < NST; s++) { mbar_init(fullb + s, 1); mbar_init(emptyb + s, T / 32); }
+			mbar_init(stashfree, T / 32);
+		}
+		__syncthreads();
+		if (t < 32) issue_burst(f0 >> FLA, 0);
+	}
+
 #pragma unroll 1
 	for (long long f = f0; f < f1; f++) {
 		c64 v[P];
@@ -272,62 +344,69 @@ wf_fft2_kernel(const Wf2Params p)
 			// itself, so no barrier is involved.  wf_split_kernel + MODE_SPLIT did the same arithmetic with a
 			// frame-sized scratch for the whole batch, i.e. a round trip of 16 B per point through HBM.
 			if constexpr (FUSED) {
-			constexpr int NA = 1 << FLA;
+			constexpr int NA = FNA;
 			constexpr int NBIG = N << FLA;
 			const int r = (int)(f & (NA - 1));
 			unsigned long long *scr = p.scratch + (size_t)blockIdx.x * (NA - 1) * N;
 			if (r == 0) {
 				typedef typename raw_word<FIN32>::type raw_t;
 				const raw_t *src = reinterpret_cast<const raw_t *>(p.raw) + (f >> FLA) * hop;
-				const unsigned long long *twb = reinterpret_cast<const unsigned long long *>(p.tw_big);
-				// loads in bursts of CH positions m, fenced from the arithmetic and the stores: one memory
-				// latency per burst instead of one per position (ptxas will not move loads above the stores)
-				// Na = 2: the one twiddle W_{2N}^m, m = n1*M + t, is W_{2N}^t (one load per frame) times the
-				// compile-time constant W_{2N/M}^{n1} = W_64^{n1}: two more FFMA2 instead of 32 loads
-				constexpr bool TWC = NA == 2 && NBIG / M == 64;
-				c64 wt = pk(1.f, 0.f);
-				if (TWC) wt = __ldg(twb + t);
-#ifndef RO_FUSED_CH
-#define RO_FUSED_CH 16
-#endif
-#ifndef RO_FUSED_CH_F32
-#define RO_FUSED_CH_F32 16
-#endif
-				constexpr int CH = (FIN32 ? RO_FUSED_CH_F32 : RO_FUSED_CH) / NA;   // float32: twice the registers per sample in flight
+				// The twiddle W_{2N}^m, m = n1*M + t, is W_{2N}^t (loaded once per frame) times the compile-time
+				// constant W_{2N/M}^{n1} = W_64^{n1}.
+				const c64 wt1 = __ldg(reinterpret_cast<const unsigned long long *>(p.tw_big) + t);
 #pragma unroll
-				for (int c0 = 0; c0 < R1; c0 += CH) {
-					raw_t raw[CH][NA];
-					float wv[CH][NA];
-					c64 bb[CH][FLA];
-					ptxas_fence(p.stagger & 1);
-#pragma unroll
-					for (int j = 0; j < CH; j++) {
-						const int m = (c0 + j) * M + t;
-#pragma unroll
-						for (int q = 0; q < NA; q++) {
-							raw[j][q] = __ldg(src + q * N + m);
-							wv[j][q] = __ldg(p.window_full + q * N + m);
+				for (int b = 0; b < NB; b++) {
+					raw_t raw[2 * HP][2];
+					float wv[2 * HP][2];
+					if (b == 0) {
+						// the stash of the previous frame has been read by every warp: bursts 1, 2 may land in it
+						if (t < 32) {
+							mbar_wait(stashfree, stashph);
+							if (NB > 1) issue_burst(f >> FLA, 1);
+							if (NB > 2) issue_burst(f >> FLA, 2);
 						}
-						if (!TWC) {
+						stashph ^= 1u;
+					} else if (b + 2 < NB && (t >> 5) == b % (T / 32)) {
+						issue_burst(f >> FLA, b + 2);
+					}
+					ptxas_fence(p.stagger & 1);
+					const int s = b % 3;
+					mbar_wait(fullb + s, (fullph >> s) & 1u);
+					fullph ^= 1u << s;
+					{
+						const unsigned char *st = stage_ptr(s);
+						const raw_t *rr = reinterpret_cast<const raw_t *>(st);
+						const float *wl = reinterpret_cast<const float *>(st + 4 * RUN_RAW), *wh = wl + HP * M;
 #pragma unroll
-							for (int i = 0; i < FLA; i++) bb[j][i] = __ldg(twb + ((m << i) & (NBIG - 1)));
+						for (int j = 0; j < HP; j++) {
+							// j: low position b*HP + j;  HP + j: high position R1 - (b+1)*HP + j
+							raw[j][0] = rr[0 * HP * M + j * M + t];
+							raw[HP + j][0] = rr[1 * HP * M + j * M + t];
+							raw[j][1] = rr[2 * HP * M + j * M + t];
+							raw[HP + j][1] = rr[3 * HP * M + j * M + t];
+							wv[j][0] = wl[j * M + t];
+							wv[HP + j][0] = wh[j * M + t];
+							wv[j][1] = wh[(HP - 1 - j) * M + (M - 1 - t)];
+							wv[HP + j][1] = wl[(HP - 1 - j) * M + (M - 1 - t)];
 						}
 					}
 					ptxas_fence(p.stagger & 1);
 #pragma unroll
-					for (int j = 0; j < CH; j++) {
-						const int m = (c0 + j) * M + t;
-						c64 xq[NA];
+					for (int jj = 0; jj < 2 * HP; jj++) {
+						const int n1 = jj < HP ? b * HP + jj : R1 - (b + 1) * HP + (jj - HP);
+						const int m = n1 * M + t;
+						c64 xq[2];
 #pragma unroll
-						for (int q = 0; q < NA; q++)
-							xq[q] = mul2(add2(raw_to_c64(raw[j][q]), gain2), pk(wv[j][q], wv[j][q]));
-						fft_dif2<NA>(xq);
-						if (TWC) xq[1] = cmul2(cmul2(xq[1], wt), cw64((c0 + j) & 31), -sw64((c0 + j) & 31));
-						else twiddle_powers2<NA>(xq, bb[j]);
-						v[c0 + j] = xq[0];
-#pragma unroll
-						for (int rr = 1; rr < NA; rr++) scr[(rr - 1) * N + m] = xq[bitrev(rr, FLA)];
+						for (int q = 0; q < 2; q++)
+							xq[q] = mul2(add2(raw_to_c64(raw[jj][q]), gain2), pk(wv[jj][q], wv[jj][q]));
+						fft_dif2<2>(xq);
+						xq[1] = cmul2(cmul2(xq[1], wt1), cw64(n1), -sw64(n1));
+						v[n1] = xq[0];
+						scr[m] = xq[1];
 					}
+					// the values are in registers and used: the stage may be refilled
+					__syncwarp();
+					if ((t & 31) == 0) mbar_arrive(emptyb + s);
 				}
 #if RO_L2_PREFETCH
 				if (f + NA < f1) {     // the hop new samples of the next frame
@@ -407,6 +486,11 @@ wf_fft2_kernel(const Wf2Params p)
 #pragma unroll
 		for (int k1 = 0; k1 < R1; k1++) S[k1 * ROW1 + t] = v[bitrev(k1, LP)];
 		__syncthreads();
+		if constexpr (FUSED) {
+			// every warp is through the load phase of this frame: the ring's own stages can take the first
+			// steps of the next frame now, a whole frame ahead of their use
+			if (t < 32 && (f & (FNA - 1)) == 0 && f + FNA < f1) issue_burst((f >> FLA) + 1, 0);
+		}
 
 		// every thread has consumed the ring for this frame: fetch the next frame's new samples
 		if (STAGE && t == 0 && f + 1 < f1) {
@@ -430,30 +514,20 @@ wf_fft2_kernel(const Wf2Params p)
 
 		// ---- pass 2 ----
 		// Row k1 of S (R2*R3 points) is read and transformed by the R3 threads (k1, n3) alone, all in one
-		// warp.  INPLACE: they write output (k2, n3) back into slot k2*R3 + n3 of the SAME row, so no
-		// thread has to wait for the loads of any other warp (the split barrier bar_rd2 was the second
-		// largest stall: every warp held its stores until the last chained warp had loaded); loads and
-		// stores of one warp reach shared memory in program order.  The 16-byte units of a slot group are
-		// XOR-permuted by k1/2 so that pass 3, whose quarter-warps read the same unit of 8 different rows,
-		// finds them in 8 different bank groups.
+		// warp; the outputs go to the transposed, XOR-swizzled layout pass 3 reads with 128-bit loads.
 		{
 			const int k1 = t / R3, n3 = t % R3;
 			if (CHAIN && (p.stagger & 2)) chain_wait(wq, wl, cdist);
 #pragma unroll
 			for (int n2 = 0; n2 < R2; n2++) v[n2] = S[k1 * ROW1 + n2 * R3 + n3];
 			if (CHAIN && (p.stagger & 2)) chain_pass(wq, wl, LEVELS, cdist);
-			if (!INPLACE) mbar_arrive(bar_rd2);         // my pass-2 inputs are in registers
+			mbar_arrive(bar_rd2);                       // my pass-2 inputs are in registers
 			fft_fwd2<R2, USE_DIT>(v);
 			RO_SITE(2, p.stagger & 1);
 			twiddle_powers2<R2>(v, b2);
 			RO_SITE(3, p.stagger & 1);
-			if (INPLACE) {
-				__syncwarp();
-				c64 *dst = S + k1 * ROW1 + (n3 ^ (((k1 >> 1) & 7) << 1));
-#pragma unroll
-				for (int k2 = 0; k2 < R2; k2++) dst[k2 * R3] = v[bitrev(k2, LP)];
-			} else {
-				mbar_wait(bar_rd2, (unsigned int)(f - f0) & 1u);   // ... and so are everyone else's
+			mbar_wait(bar_rd2, (unsigned int)(f - f0) & 1u);   // ... and so are everyone else's
+			{
 				const int col = k1 ^ (n3 * SW);
 #pragma unroll
 				for (int k2 = 0; k2 < R2; k2++) S[(k2 * R3 + n3) * R1 + col] = v[bitrev(k2, LP)];
@@ -471,20 +545,6 @@ wf_fft2_kernel(const Wf2Params p)
 			const int k1b = pbase % R1, k2 = pbase / R1;
 			c64 (&u)[P] = v;                       // u[c*R3 + n3]
 			if (CHAIN && (p.stagger & 4)) chain_wait(wq, wl, cdist3);
-			if (INPLACE) {
-				// row k1b + c, slots k2*R3 .. k2*R3 + R3-1: R3/2 128-bit loads, unit L sits at L ^ (k1/2 & 7)
-#pragma unroll
-				for (int c = 0; c < G; c++) {
-					const int k1 = k1b + c;
-					const unsigned int a0 = (unsigned int)((k1 * ROW1 + k2 * R3) * 8) ^ (unsigned int)(((k1 >> 1) & 7) << 4);
-#pragma unroll
-					for (int L = 0; L < R3 / 2; L++) {
-						const ulonglong2 q = *reinterpret_cast<const ulonglong2 *>(reinterpret_cast<const unsigned char *>(S) + (a0 ^ (unsigned int)(L << 4)));
-						u[c * R3 + 2 * L] = q.x;
-						u[c * R3 + 2 * L + 1] = q.y;
-					}
-				}
-			} else {
 #pragma unroll
 			for (int n3 = 0; n3 < R3; n3++) {
 				constexpr int GM = G - 1;
@@ -496,7 +556,6 @@ wf_fft2_kernel(const Wf2Params p)
 					u[((2 * h2) ^ (sw & GM)) * R3 + n3] = q.x;
 					u[((2 * h2 + 1) ^ (sw & GM)) * R3 + n3] = q.y;
 				}
-			}
 			}
 			if (CHAIN && (p.stagger & 4)) chain_pass(wq, wl, LEVELS, cdist3);
 			mbar_arrive(bar_rd3);                      // my pass-3 inputs are in registers
@@ -541,14 +600,14 @@ wf_fft2_kernel(const Wf2Params p)
 							for (int c = 0; c < G; c++) ev[c] = stash[(k3 * G + c) * T + t];
 							const int k = k3 * (N / R3) + G * t;
 							if (G == 2 && la == 1) {
-								// float32 fused 32k (-DRO_ROWS_STCS=1): evict-first stores, so that the rows do not
-								// push the overlapped input (re-read by the next frame) out of L2
+								// fused 32k (-DRO_ROWS_STCS=1): evict-first stores, so that the rows do not push the
+								// overlapped input (re-read by the next frame) and the parked classes out of L2
 #ifndef RO_ROWS_STCS
 #define RO_ROWS_STCS 0
 #endif
 								float4 *dst = reinterpret_cast<float4 *>(row + (((k << 1) + big_half) & big_mask));
 								const float4 val = make_float4(ev[0], mag[k3][0], ev[1], mag[k3][1]);
-								if (FIN32 && RO_ROWS_STCS) __stcs(dst, val);
+								if (FUSED && RO_ROWS_STCS) __stcs(dst, val);
 								else *dst = val;
 							} else {
 #pragma unroll
@@ -567,6 +626,13 @@ wf_fft2_kernel(const Wf2Params p)
 						row[((k << la) + r + big_half) & big_mask] = mag[k3][c];
 					}
 				}
+				}
+				if constexpr (FUSED) {
+					// the last class of the frame has read the stash: its 64 KB may stage the next frame
+					if (r == FNA - 1) {
+						__syncwarp();
+						if ((t & 31) == 0) mbar_arrive(stashfree);
+					}
 				}
 			} else {
 			float *row = p.rows + f * p.row_stride + G * t;

@@ -31,7 +31,6 @@ bool pick_one(int mode, bool gain, V2Kernel *k)
 
 bool v2_pick(int log2n, int mode, bool gain, V2Kernel *out)
 {
-	if (mode == V2_FUSED2) return false;         // measured slower than the split path at 64k: not instantiated
 	if (mode == V2_FUSED1) {
 		if (log2n != 14) return false;
 		out->log2n = log2n;
@@ -115,7 +114,7 @@ cudaError_t v2_launch_fused(const V2Kernel &k, int grid, cudaStream_t s, const v
                             long long row_stride, long long n_frames, long long hop, long long frames_per_cta,
                             float iq_gain, int pair, int stagger)
 {
-	const int la = k.mode == V2_FUSED1_F32 ? 1 : k.mode - V2_FUSED1 + 1;
+	const int la = 1;
 	Wf2Params p;
 	p.iq = NULL;
 	p.window_half = NULL;

@@ -5,7 +5,7 @@
 
 namespace ro {
 
-enum { V2_DIRECT = 0, V2_STAGED = 1, V2_SPLIT = 2, V2_FUSED1 = 3, V2_FUSED2 = 4, V2_DIRECT_F32 = 5, V2_FUSED1_F32 = 6 };   // = MODE_* of ro_kernels2.cuh
+enum { V2_DIRECT = 0, V2_STAGED = 1, V2_SPLIT = 2, V2_FUSED1 = 3, V2_DIRECT_F32 = 5, V2_FUSED1_F32 = 6 };   // = MODE_* of ro_kernels2.cuh
 
 struct V2Kernel {
 	const void *fn;      // kernel symbol (for attribute / occupancy queries)
@@ -22,7 +22,7 @@ bool v2_pick(int log2n, int mode, bool gain, V2Kernel *out);
 
 // The same for float32 I/Q input (N = 1024 .. 16384), launched with v2_launch like V2_DIRECT (ro_v2f.cu).
 bool v2_pick_f32(int log2n, bool gain, V2Kernel *out);
-// V2_FUSED1 for float32 I/Q (frames of 2*16384 points), launched with v2_launch_fused; d_raw 8-byte aligned.
+// V2_FUSED1 for float32 I/Q (frames of 2*16384 points), launched with v2_launch_fused.
 bool v2_pick_fused_f32(V2Kernel *out);
 
 // Launches it: n_frames items of `hop`-spaced N-sample windows of d_iq (int16 I/Q), or, for
@@ -33,8 +33,10 @@ cudaError_t v2_launch(const V2Kernel &k, int grid, cudaStream_t s, const void *d
                       const float2 *d_tw, float *d_rows, long long row_stride, long long n_frames, long long hop,
                       long long frames_per_cta, float iq_gain, int log2na, int pair, int stagger);
 
-// V2_FUSED1 / V2_FUSED2 (frames of 2*16384 / 4*16384 points, int16 input): one launch does the radix-Na
-// step and the Na 16k transforms of each frame; d_scratch holds grid * (Na-1) * 16384 packed complex.
+// V2_FUSED1 (frames of 2*16384 points): one launch does the radix-2 step and the two 16k transforms of each
+// frame; d_scratch holds grid * 16384 packed complex.  The raw samples and the first half of the window
+// (which must be symmetric) reach shared memory by cp.async.bulk: d_raw and every frame start
+// (hop * bytes per sample) must be 16-byte aligned, rows 16-byte aligned (pair = 1).
 cudaError_t v2_launch_fused(const V2Kernel &k, int grid, cudaStream_t s, const void *d_raw, const float *d_window_full,
                             const float2 *d_tw_big, const float2 *d_tw_nb, void *d_scratch, float *d_rows,
                             long long row_stride, long long n_frames, long long hop, long long frames_per_cta,

@@ -41,6 +41,28 @@ def test_rows_match_oracle_int16(bins, overlap):
     wf.close()
 
 
+@pytest.mark.parametrize("bins,overlap,iq_gain", [
+    (1024, 512, 7.0), (4096, 3072, -11.5), (4096, 4093, 0.75), (8192, 6144, 3.0), (16384, 12288, 250.0),
+    (16384, 12289, -0.5), (32768, 24576, 40.0), (32768, 24575, 1.0), (65536, 49152, -120.0), (131072, 65536, 9.0),
+])
+def test_rows_match_oracle_int16_with_iq_gain(bins, overlap, iq_gain):
+    """A2 on the WAV encoding: int16 I/Q with iq_gain != 0, additive on Q before the window
+    (src/FFTBackend.cpp:53-92), through every int16 kernel variant: the TMA-staged ring (aligned hop),
+    direct loads (odd hop), the fused long-frame kernels (32k, 64k), the split path (odd hop, 128k)."""
+    hop = bins - overlap
+    n = bins + 9 * hop + min(11, hop - 1)
+    iq = station_iq(n, 96000, seed=bins + overlap + 1)
+    wf = ro.Waterfall(bins, overlap, sample_rate=96000, in_format=ro.IN_INT16, iq_gain=iq_gain)
+    rows, _, nf = wf.process_host(iq)
+    wf.close()
+    ref = R.waterfall_rows(iq, bins, overlap, iq_gain=iq_gain)
+    assert nf == len(ref) == 10
+    assert_rows_close(rows, ref, f"int16 + gain N={bins} ov={overlap}")
+    # and the gain is really applied: the rows differ from the gain-free ones
+    ref0 = R.waterfall_rows(iq, bins, overlap)
+    assert np.abs(ref - ref0).max() > 0
+
+
 @pytest.mark.parametrize("bins,overlap", [(131072, 65536), (524288, 262144)])
 def test_rows_match_oracle_large(bins, overlap):
     n = bins * 2 + 77
@@ -105,6 +127,33 @@ def test_float32_32k_fused_many_frames_per_cta(overlap, iq_gain, monkeypatch):
     assert nf2 == nf
     assert_rows_close(rows2, ref, "float32 split N=32768")
     assert_rows_close(rows, rows2.astype(np.float64), "fused against split")
+
+
+@pytest.mark.parametrize("bins,fmt,overlap,iq_gain", [
+    (32768, "int16", 24576, 0.0), (32768, "int16", 0, 2.5), (65536, "int16", 49152, 0.0),
+    (65536, "int16", 32768, -3.0), (65536, "float32", 49152, 0.125), (65536, "int16", 65536 - 16381, 0.0),
+])
+def test_fused_long_frames_many_frames_per_cta(bins, fmt, overlap, iq_gain):
+    """32k and 64k frames run in ONE kernel (MODE_FUSED*: the samples and the window reach shared memory
+    through a ring of cp.async.bulk stages, radix-2/4 step, then 2/4 16k transforms per frame).  Enough
+    frames that every CTA of the persistent grid walks several of them: the ring's mbarrier phases, the
+    stages that live in the magnitude stash and the CTA-private scratch are all reused.  The last case
+    has a hop that is not a multiple of 4 samples: no 16-byte aligned frame starts, so the split path
+    runs instead and must give the same rows."""
+    hop = bins - overlap
+    n_frames = 148 * 4 + 37 if hop <= 16384 else 200
+    n = bins + (n_frames - 1) * hop + 3
+    spec = synth.SynthSpec(sample_rate=96000, n_samples=n, seed=bins // 1024 + overlap % 97, carrier_freq=21999.7)
+    if fmt == "int16":
+        iq, in_format = synth.generate_int16(spec), ro.IN_INT16
+    else:
+        iq, in_format = synth.generate_float32(spec), ro.IN_FLOAT32
+    wf = ro.Waterfall(bins, overlap, sample_rate=96000, in_format=in_format, iq_gain=iq_gain)
+    rows, _, nf = wf.process_host(iq)
+    wf.close()
+    ref = R.waterfall_rows(iq, bins, overlap, iq_gain=iq_gain)
+    assert nf == len(ref) == n_frames
+    assert_rows_close(rows, ref, f"{fmt} fused N={bins} ov={overlap}")
 
 
 def test_complex64_input_is_narrowed_like_float32():
