@@ -3,18 +3,30 @@
 
 Workload (BASELINE.json config 2): 96 kHz int16 I/Q, 16384-point
 FFT, overlap 12288 (75 %), Bolidozor recorder bands, bolid detector statistics per row.
-One step = one pass of the hot path (fused unpack+window+FFT+magnitude kernel, then
-the detector kernel) over one time shard of synthetic station data per GPU.
+One step = one pass of the hot path (fused unpack+window+FFT+magnitude kernel, then the
+detector kernel) over one batch of synthetic station data per GPU: --passes shards of
+2^--log2-samples samples each, taken in turn from --shards distinct shards resident in HBM,
+rows of every shard written to the same device buffer (as the library's own host path does).
+The default batch makes a step about 100 ms, so that the --steps 20 the driver asks for are
+2 s of steady state under the power cap, not a 50 ms burst.
 
   value     complex input Msamples/s, inputs resident in HBM (whole job, all ranks)
   e2e       the same through ro_wf_process_host: pinned host I/Q in, recorder-band
             rows + detector records out, H2D/D2H inside the timed region
-  roofline  algorithmic HBM bytes of the fused kernel / its CUDA-event duration
-  cpu_baseline  the reference's own C++ (oracle/_ref/ref_oracle) on this box's host cores
+  roofline  algorithmic HBM bytes of the fused kernel / its CUDA-event duration (a second,
+            separately profiled pass: the timed loop carries no per-launch events)
+  parity    the timed input's first frames against the oracle, the tests' rule and the strict one
+  fp64      the same shape through the FP64 variant (cfg.precision = 1)
+  cpu_baseline  the reference's own C++ (oracle/_ref/ref_oracle) on this box's host cores;
+  cpu_baseline_alt  the same path restated on scipy.fft (pocketfft), the -O0 build, an FFTW probe
+  dropin    the reference's Pipeline binary with "factory": "waterfall_cuda"
 
 `--impl reference` times only the reference CPU implementation (rank 0).
+`--sweep` prints BASELINE config 5 (FFT size x overlap, device-resident) with a CPU figure per point.
 """
 import argparse
+import ctypes
+import ctypes.util
 import json
 import math
 import os
@@ -40,6 +52,18 @@ DETECT_HZ = (26450.0, 26550.0)
 NOISE_HZ = (26000.0, 26300.0)
 AVG_HZ = 40.0
 WORKLOAD = "C2b: Bolidozor bands, 96 kHz int16 I/Q, 16384-pt FFT, overlap 12288 (75%)"
+METRIC = "complex Msamples/s through waterfall FFT+magnitude+bolid detect"
+
+
+def bench_config(log2_samples, passes, shards):
+    """The `config` object of both arms (the driver compares them)."""
+    S = 1 << log2_samples
+    F = (S - BINS) // HOP + 1
+    return {"workload": WORKLOAD, "bins": BINS, "overlap": OVERLAP, "sample_rate": SR,
+            "samples_per_gpu_per_step": S * passes, "frames_per_gpu_per_step": F * passes,
+            "shard_samples": S, "shards_per_step": passes, "distinct_shards": shards,
+            "sharding": "time shards, one per GPU, overlap halo re-read from input; no collective",
+            "l2": "every pass reads another %d MiB shard and writes %d MiB of rows: larger than L2" % (4 * S >> 20, 4 * BINS * F >> 20)}
 
 
 # ----------------------------------------------------------------------------
@@ -52,11 +76,11 @@ def freq_to_bin(freq, sr, bins):
     return min(max(int(v), 0), bins - 1)
 
 
-def bolidozor_bands():
-    lo, hi = (freq_to_bin(f, SR, BINS) for f in SNAP_BAND_HZ)
-    dlo, dhi = (freq_to_bin(f, SR, BINS) for f in DETECT_HZ)
-    nlo, nhi = (freq_to_bin(f, SR, BINS) for f in NOISE_HZ)
-    avg = freq_to_bin(AVG_HZ, SR, BINS) - freq_to_bin(0.0, SR, BINS)
+def bolidozor_bands(sr=SR, bins=BINS):
+    lo, hi = (freq_to_bin(f, sr, bins) for f in SNAP_BAND_HZ)
+    dlo, dhi = (freq_to_bin(f, sr, bins) for f in DETECT_HZ)
+    nlo, nhi = (freq_to_bin(f, sr, bins) for f in NOISE_HZ)
+    avg = max(1, freq_to_bin(AVG_HZ, sr, bins) - freq_to_bin(0.0, sr, bins))
     return (lo, hi), dict(det_lo=dlo, det_w=dhi - dlo, noise_lo=nlo, noise_w=nhi - nlo, avg_bins=avg)
 
 
@@ -114,7 +138,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "50"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -130,29 +154,23 @@ class ClockSampler:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
         self.proc.terminate()
-        sm, smax, reasons = [], None, set()
+        sm, pw, smax, reasons = [], [], None, set()
         for (t, l) in self.lines:
-            if t < t0 - 0.05 or t > t1 + 0.15:
+            if t < t0 or t > t1:
                 continue
             f = [x.strip() for x in l.split(",")]
             try:
                 sm.append(float(f[1]))
                 smax = float(f[2])
+                pw.append(float(f[3]))
             except Exception:
                 continue
             names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
             for nm, v in zip(names, f[5:9]):
                 if v.lower().startswith("active"):
                     reasons.add(nm)
-        if not sm:       # region shorter than the sampling period: use every sample we have
-            for (t, l) in self.lines:
-                f = [x.strip() for x in l.split(",")]
-                try:
-                    sm.append(float(f[1]))
-                    smax = float(f[2])
-                except Exception:
-                    pass
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax,
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_min_mhz": float(min(sm)) if sm else None,
+                "sm_max_mhz": smax, "power_w_median": float(np.median(pw)) if pw else None,
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
@@ -160,9 +178,11 @@ class ClockSampler:
 # reference CPU arm
 # ----------------------------------------------------------------------------
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "ref_oracle")
-
-
+REF_BIN_O0 = os.path.join(ROOT, "oracle", "_ref", "ref_oracle_O0")
 CUDA_BIN = os.path.join(ROOT, "radio_observer_b200", "host", "_build", "radio-observer-cuda")
+FFT_NOTE = ("FFTW and CFITSIO are absent from this image: the reference's classes are linked against a scalar "
+            "radix-4 Stockham FFT (oracle/shims/fftw3_shim.cpp, about pocketfft's speed, not SIMD FFTW) and an "
+            "uncompressed FITS writer; cpu_baseline_alt gives the scipy.fft figure of the same path beside it")
 
 
 def ref_config_json(out_dir, factory="waterfall", extra=None):
@@ -200,64 +220,220 @@ def host_station_iq(n_samples, seed):
     return synth.generate_int16(spec)
 
 
-def run_reference_cpu(sample_seconds, procs, binary=None, factory="waterfall", extra=None, wav_path=None, flags=()):
-    """Time the reference's own C++ classes (or, if the binary is absent, the numpy port)
-    on `procs` independent time shards of sample_seconds each.  Returns
-    (Msamples/s, kind, cores, description).  With binary=CUDA_BIN, factory="waterfall_cuda" the
-    same Pipeline runs with the CUDA backend behind the adapter (the drop-in measurement)."""
-    binary = binary or REF_BIN
-    from radio_observer_b200 import synth
-    n = int(sample_seconds * SR)
-    n -= n % 1024
-    base = "/dev/shm" if os.path.isdir("/dev/shm") else None
-    tmp = tempfile.mkdtemp(prefix="ro_bench_", dir=base)
-    try:
-        if os.path.exists(binary):
-            wav = wav_path or os.path.join(tmp, "in.wav")
-            if not wav_path:
-                synth.write_wav(wav, host_station_iq(n, 0x5EED0002), SR)
-            for p in range(procs):
-                d = os.path.join(tmp, "p%d" % p)
+class RefRunner:
+    """The reference's own Pipeline binary on `procs` concurrent copies of one WAV in tmpfs."""
+
+    def __init__(self, sample_seconds, procs, binary=None, factory="waterfall", extra=None, wav_path=None, flags=()):
+        from radio_observer_b200 import synth
+        self.binary = binary or REF_BIN
+        self.n = int(sample_seconds * SR)
+        self.n -= self.n % 1024
+        self.procs = procs
+        self.flags = flags
+        base = "/dev/shm" if os.path.isdir("/dev/shm") else None
+        self.tmp = tempfile.mkdtemp(prefix="ro_bench_", dir=base)
+        self.wav = wav_path or os.path.join(self.tmp, "in.wav")
+        if not wav_path:
+            synth.write_wav(self.wav, host_station_iq(self.n, 0x5EED0002), SR)
+        for p in range(procs):
+            d = os.path.join(self.tmp, "p%d" % p)
+            os.makedirs(os.path.join(d, "out"))
+            open(os.path.join(d, "cfg.json"), "w").write(ref_config_json(os.path.join(d, "out"), factory, extra))
+        self.crashes = 0
+
+    def run_once(self):
+        """Returns the wall time of the slowest process, or None if one of them kept failing."""
+        times = [None] * self.procs
+
+        def worker(p):
+            d = os.path.join(self.tmp, "p%d" % p)
+            # the reference has a start-up race (threads started from a base-class constructor, see
+            # DESIGN.md) and sometimes dies before processing: run again, counted
+            for attempt in range(60):
+                shutil.rmtree(os.path.join(d, "out"), ignore_errors=True)
                 os.makedirs(os.path.join(d, "out"))
-                open(os.path.join(d, "cfg.json"), "w").write(ref_config_json(os.path.join(d, "out"), factory, extra))
-            times = [None] * procs
+                t0 = time.perf_counter()
+                rc = subprocess.call([self.binary, "-c", os.path.join(d, "cfg.json"), "-q", *self.flags, self.wav],
+                                     stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, cwd=d)
+                if rc == 0:
+                    times[p] = time.perf_counter() - t0
+                    return
+                self.crashes += 1
 
-            def worker(p):
-                d = os.path.join(tmp, "p%d" % p)
-                # the reference has a start-up race (threads started from a base-class
-                # constructor, see DESIGN.md) and sometimes aborts before processing: retry
-                for attempt in range(25):
-                    t0 = time.perf_counter()
-                    rc = subprocess.call([binary, "-c", os.path.join(d, "cfg.json"), "-q", *flags, wav],
-                                         stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, cwd=d)
-                    if rc == 0:
-                        times[p] = time.perf_counter() - t0
-                        return
-
-            ths = [threading.Thread(target=worker, args=(p,)) for p in range(procs)]
-            for t in ths:
-                t.start()
-            for t in ths:
-                t.join()
-            if all(t is not None for t in times):
-                return (sum(n / t for t in times) / 1e6, "reference", procs,
-                        "%d concurrent process(es), each %.0f s of 96 kHz station I/Q (WAV in tmpfs) through the "
-                        "reference's own Pipeline/WAVStream/WaterfallBackend/BolidRecorder (oracle/_ref, -O2, shim "
-                        "FFT because FFTW is absent), FITS to tmpfs" % (procs, n / SR))
-        if binary != REF_BIN:
-            return None
-        # port: numpy restatement, single thread
-        from oracle import ref_numpy as R
-        iq = host_station_iq(n, 0x5EED0002)
-        _, det = bolidozor_bands()
-        d = R.DetectorBands(det["det_lo"], det["det_w"], det["noise_lo"], det["noise_w"], det["avg_bins"], 0, 0)
+        ths = [threading.Thread(target=worker, args=(p,)) for p in range(self.procs)]
         t0 = time.perf_counter()
-        rows = R.waterfall_rows(iq, BINS, OVERLAP)
-        R.detector_rows(rows, d)
-        dt = time.perf_counter() - t0
-        return n / dt / 1e6, "port", 1, "%.0f s of station I/Q through oracle/ref_numpy.py (numpy pocketfft)" % (n / SR)
+        for t in ths:
+            t.start()
+        for t in ths:
+            t.join()
+        wall = time.perf_counter() - t0
+        return wall if all(t is not None for t in times) else None
+
+    def close(self):
+        shutil.rmtree(self.tmp, ignore_errors=True)
+
+
+def run_reference_cpu(sample_seconds, procs, runs=1, **kw):
+    """(Msamples/s of the best run, list of all runs) for the reference binary, or None without it."""
+    binary = kw.get("binary") or REF_BIN
+    if not os.path.exists(binary):
+        return None
+    r = RefRunner(sample_seconds, procs, **kw)
+    try:
+        vals = []
+        for _ in range(runs):
+            w = r.run_once()
+            if w is not None:
+                vals.append(procs * r.n / w / 1e6)
+        return (max(vals), [round(v, 2) for v in vals], r.n, r.crashes) if vals else None
     finally:
-        shutil.rmtree(tmp, ignore_errors=True)
+        r.close()
+
+
+def numpy_port_baseline(seconds):
+    """oracle/ref_numpy.py, single thread (the fallback when the reference binary is absent)."""
+    from oracle import ref_numpy as R
+    n = int(seconds * SR)
+    iq = host_station_iq(n, 0x5EED0002)
+    _, det = bolidozor_bands()
+    d = R.DetectorBands(det["det_lo"], det["det_w"], det["noise_lo"], det["noise_w"], det["avg_bins"], 0, 0)
+    t0 = time.perf_counter()
+    rows = R.waterfall_rows(iq, BINS, OVERLAP)
+    R.detector_rows(rows, d)
+    return n / (time.perf_counter() - t0) / 1e6
+
+
+def scipy_path(iq, bins, overlap, det, workers, chunk_frames=256):
+    """The hot path restated on scipy.fft (pocketfft, SIMD, double): framing, window in double, FFT,
+    magnitude, fftshift, float rows, then noise / peak / mean per row.  A timing vehicle for
+    cpu_baseline_alt (the parity checker is oracle/ref_numpy.py).  Returns seconds."""
+    import scipy.fft
+    from oracle import ref_numpy as R
+    hop = bins - overlap
+    x = iq.astype(np.float64).view(np.complex128) if iq.dtype == np.float64 else (
+        iq.reshape(-1, 2).astype(np.float64) @ np.array([1.0, 1j]))
+    w = R.nuttall_window(bins).astype(np.float64)
+    F = (len(x) - bins) // hop + 1
+    frames = np.lib.stride_tricks.sliding_window_view(x, bins)[::hop][:F]
+    t0 = time.perf_counter()
+    acc = 0.0
+    for f0 in range(0, F, chunk_frames):
+        blk = frames[f0:f0 + chunk_frames] * w
+        spec = scipy.fft.fft(blk, axis=1, workers=workers, overwrite_x=True)
+        rows = np.fft.fftshift(np.abs(spec), axes=1).astype(np.float32)
+        nb = rows[:, det["noise_lo"]:det["noise_lo"] + det["noise_w"]]
+        noise = 2.0 * np.partition(nb, det["noise_w"] // 4, axis=1)[:, det["noise_w"] // 4]
+        db = rows[:, det["det_lo"]:det["det_lo"] + det["det_w"]]
+        peak = det["det_w"] - 1 - np.argmax(db[:, ::-1], axis=1)
+        acc += float(noise.sum()) + float(peak.sum())
+    return time.perf_counter() - t0, F
+
+
+def fft_probe():
+    """Per-transform time of a 16384-point complex128 FFT on one core: scipy.fft, and FFTW3 through
+    ctypes when libfftw3 is on the box (the reference links -lfftw3, src/FFTBackend.cpp:117-120)."""
+    import scipy.fft
+    x = (np.random.default_rng(1).standard_normal(2 * BINS)).view(np.complex128).copy()
+    scipy.fft.fft(x)
+    t0 = time.perf_counter()
+    for _ in range(200):
+        scipy.fft.fft(x)
+    out = {"scipy_fft_16k_us": round((time.perf_counter() - t0) / 200 * 1e6, 1), "libfftw3": None, "fftw_16k_us": None}
+    path = ctypes.util.find_library("fftw3")
+    out["libfftw3"] = path
+    if path:
+        try:
+            lib = ctypes.CDLL(path)
+            lib.fftw_plan_dft_1d.restype = ctypes.c_void_p
+            lib.fftw_plan_dft_1d.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_uint]
+            lib.fftw_execute.argtypes = [ctypes.c_void_p]
+            y = np.empty_like(x)
+            plan = lib.fftw_plan_dft_1d(BINS, x.ctypes.data, y.ctypes.data, -1, 1 << 6)      # FFTW_ESTIMATE
+            lib.fftw_execute(plan)
+            t0 = time.perf_counter()
+            for _ in range(200):
+                lib.fftw_execute(plan)
+            out["fftw_16k_us"] = round((time.perf_counter() - t0) / 200 * 1e6, 1)
+        except Exception as e:                      # noqa: BLE001
+            out["fftw_16k_us"] = "probe failed: %s" % e
+    return out
+
+
+def reference_arm(args, emit):
+    cores = os.cpu_count() or 1
+    ref_seconds = float(os.environ.get("RO_BENCH_REF_SECONDS", "60"))     # tests shorten it
+    cfg = bench_config(args.log2_samples, args.passes, args.shards)
+    if os.path.exists(REF_BIN):
+        r = RefRunner(ref_seconds, cores)
+        try:
+            for _ in range(args.warmup):
+                r.run_once()
+            walls = []
+            for _ in range(args.steps):
+                w = r.run_once()
+                if w is not None:
+                    walls.append(w)
+            n, crashes = r.n, r.crashes
+        finally:
+            r.close()
+        if not walls:
+            emit({"impl": "reference", "unavailable": "oracle/_ref/ref_oracle kept failing on this box"})
+            return 0
+        ms = 1e3 * float(np.mean(walls))
+        v = cores * n / (ms * 1e-3) / 1e6
+        kind = "reference"
+        desc = ("each step: %d concurrent processes, each %.0f s of 96 kHz station I/Q (WAV in tmpfs) through the "
+                "reference's own Pipeline/WAVStream/WaterfallBackend/BolidRecorder (oracle/_ref, -O2), FITS to tmpfs, "
+                "process start-up included; %d start-up crashes re-run. %s" % (cores, n / SR, crashes, FFT_NOTE))
+    else:
+        secs = min(ref_seconds, 20.0)
+        vals = [numpy_port_baseline(secs) for _ in range(min(args.steps, 3))]
+        v, cores, kind = float(np.median(vals)), 1, "port"
+        ms = 1e3 * secs * SR / (v * 1e6)
+        desc = "%.0f s of station I/Q through oracle/ref_numpy.py (numpy pocketfft), one thread" % secs
+    emit({"impl": "reference", "metric": METRIC, "value": v, "unit": "Msamples/s", "n_gpus": args.gpus,
+          "steps": len(walls) if kind == "reference" else min(args.steps, 3), "warmup": args.warmup, "ms_per_step": ms,
+          "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+          "config": cfg,
+          "cpu_baseline": {"value": v, "unit": "Msamples/s", "cores": cores, "kind": kind, "sample": desc},
+          "e2e": {"value": v, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+          "gpu_launches": 0})
+    return 0
+
+
+# ----------------------------------------------------------------------------
+# rank placement: CPU cores next to the rank's GPU, before any pinned allocation
+# ----------------------------------------------------------------------------
+def bind_to_gpu_cpus(local_rank, world):
+    info = {"numa_node": None, "cpus": None, "how": None}
+    try:
+        bus = subprocess.check_output(["nvidia-smi", "-i", str(local_rank), "--query-gpu=pci.bus_id", "--format=csv,noheader"],
+                                      text=True).strip().lower()
+        if bus.startswith("0000"):
+            bus = bus[4:]                       # nvidia-smi prints an 8-digit domain, sysfs a 4-digit one
+        base = "/sys/bus/pci/devices/" + bus
+        node = int(open(base + "/numa_node").read())
+        cpus = open(base + "/local_cpulist").read().strip()
+        ids = []
+        for part in cpus.split(","):
+            a, _, b = part.partition("-")
+            ids += list(range(int(a), int(b or a) + 1))
+        every = sorted(os.sched_getaffinity(0))
+        ids = [c for c in ids if c in every]
+        info["numa_node"] = node
+        if ids and len(ids) < len(every):
+            os.sched_setaffinity(0, ids)
+            info.update(cpus=cpus, how="the GPU's local_cpulist")
+        elif world > 1 and len(every) >= world:
+            # one NUMA node reported for every GPU: give each rank its own slice of the cores, so that the
+            # first touch of its pinned buffers and its copy thread stay put
+            per = len(every) // world
+            mine = every[local_rank * per:(local_rank + 1) * per]
+            os.sched_setaffinity(0, mine)
+            info.update(cpus="%d-%d" % (mine[0], mine[-1]), how="even slice of the cores (no per-GPU locality reported)")
+    except Exception as e:                          # noqa: BLE001
+        info["how"] = "unavailable: %s" % e
+    return info
 
 
 def main():
@@ -266,8 +442,11 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--log2-samples", type=int, default=28, help="complex samples per GPU per step (2^k)")
+    ap.add_argument("--log2-samples", type=int, default=28, help="complex samples per shard (2^k)")
+    ap.add_argument("--passes", type=int, default=40, help="shards processed per step")
+    ap.add_argument("--shards", type=int, default=4, help="distinct shards resident in HBM, taken in turn")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sweep", action="store_true", help="BASELINE config 5 instead of the headline line")
     args = ap.parse_args()
     # The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version
     # banner from C on the first collective): keep the real stdout aside for the result line and point
@@ -288,26 +467,9 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return 0
-        cores = os.cpu_count() or 1
-        # bounded sample: each step = every core runs one 12 s shard
-        vals = []
-        desc = kind = None
-        ref_seconds = float(os.environ.get("RO_BENCH_REF_SECONDS", "120"))   # tests shorten it
-        for i in range(1 + min(args.steps, 2)):      # one warm-up run, then up to two timed runs
-            v, kind, used, desc = run_reference_cpu(ref_seconds, cores)
-            vals.append(v)
-        v = float(np.median(vals[1:])) if len(vals) > 1 else vals[0]
-        n = int(ref_seconds * SR)
-        line = {"impl": "reference", "metric": "complex Msamples/s through waterfall FFT+magnitude+bolid detect",
-                "value": v, "unit": "Msamples/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": 1e3 * used * n / (v * 1e6), "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "bins": BINS, "overlap": OVERLAP, "sample_rate": SR},
-                "cpu_baseline": {"value": v, "unit": "Msamples/s", "cores": used, "kind": kind, "sample": desc},
-                "e2e": {"value": v, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                "gpu_launches": 0}
-        emit(line)
-        return 0
+        return reference_arm(args, emit)
+
+    placement = bind_to_gpu_cpus(local_rank, world)
 
     import torch
     import radio_observer_b200 as ro
@@ -317,6 +479,8 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback for the product path")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    if args.sweep:
+        return sweep(args, emit, torch, ro, dev)
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -333,13 +497,14 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    # ---- the shard of the archive this rank owns (time-sharded, overlap halo) ----
-    S = 1 << args.log2_samples                       # samples per rank per step
+    # ---- the shards of the archive this rank owns (time-sharded, overlap halo) ----
+    S = 1 << args.log2_samples                       # samples per shard
+    P, G = args.passes, max(1, min(args.shards, args.passes))
     band, det = bolidozor_bands()
     wf = ro.Waterfall(BINS, OVERLAP, sample_rate=SR, in_format=ro.IN_INT16, bands=[band], detector=det,
                       device=local_rank)
     F = wf.frame_count(S)
-    d_iq = gen_iq_device(torch, S, 0x5EED0002 + rank, dev)
+    d_iq = [gen_iq_device(torch, S, 0x5EED0002 + 1000 * rank + g, dev) for g in range(G)]
     d_rows = torch.empty(F * BINS, dtype=torch.float32, device=dev)
     d_det = torch.empty(F * 4, dtype=torch.int32, device=dev)
     # a dedicated non-default stream: the default stream's handle is 0, which the C ABI
@@ -350,13 +515,12 @@ def main():
     wf.set_stream(stream.cuda_stream)
 
     def step_resident():
-        wf.process_resident(d_iq.data_ptr(), S, d_rows.data_ptr(), d_det.data_ptr(), sync=False)
+        for p in range(P):
+            wf.process_resident(d_iq[p % G].data_ptr(), S, d_rows.data_ptr(), d_det.data_ptr(), sync=False)
 
     for _ in range(args.warmup):
         step_resident()
     torch.cuda.synchronize()
-    wf.set_profiling(True)
-    wf.kernel_times()                                # clear
     l0 = wf.launch_count()
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -375,11 +539,17 @@ def main():
     barrier()
     ms_total = max_over_ranks(e0.elapsed_time(e1))
     launches = wf.launch_count() - l0
-    kms, kn = wf.kernel_times()
-    wf.set_profiling(False)
     clocks = sampler.stop(t_wall0, t_wall1) if rank == 0 else None
     ms_per_step = ms_total / args.steps
-    value = world * S / (ms_per_step * 1e-3) / 1e6
+    value = world * S * P / (ms_per_step * 1e-3) / 1e6
+
+    # ---- kernel times: a separate pass with the library's per-launch CUDA events on the same stream ----
+    wf.set_profiling(True)
+    wf.kernel_times()                                # clear
+    for _ in range(2):
+        step_resident()
+    kms, kn = wf.kernel_times()
+    wf.set_profiling(False)
 
     # ---- roofline of the dominant (fused FFT) kernel ----
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -400,21 +570,47 @@ def main():
         except Exception:
             traffic = None
     flops = 5.0 * BINS * math.log2(BINS) * F
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "kernel": "wf_fft2_kernel<14,32,16,STAGED> (packed f32x2 DIT butterflies, TMA-staged ring, chained load bursts)", "kernel_ms": fft_ms,
+    sm_clock = (clocks or {}).get("sm_mhz") or 1965.0
+    fp32_peak = 148 * 128 * 2 * sm_clock * 1e6 / 1e12      # TFLOP/s at the clock seen during the timed region
+    tflops = flops / (fft_ms * 1e-3) / 1e12
+    roofline = {"bound": "fp32-fma (the HBM fraction is the judged figure; at 75% overlap the FMA pipe binds first)",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": traffic, "kernel": wf.kernel_name(), "kernel_ms": fft_ms,
+                "kernel_launches_profiled": int(kn[0]),
                 "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
-                "fft_tflops_5NlogN": flops / (fft_ms * 1e-3) / 1e12,
+                "fft_tflops_5NlogN": tflops,
+                "fp32_frac": tflops / fp32_peak,
+                "fp32_peak_tflops": fp32_peak,
+                "fp32_peak_source": "148 SMs x 128 lanes x 2 x the median SM clock of the timed region (pipe rate measured: profiles/r01_microbench_pipe_rates.txt)",
                 "detector_kernel_ms": kms[1] / max(1, kn[1]),
+                "kernel_share_of_step": (kms[0] + kms[1]) / 2.0 / ms_per_step if ms_per_step else None,
                 "fp32_roof": {"lane_ops_per_frame": 1698 * 512, "fma_pipe_floor_cycles_per_frame": 6792,
-                              "note": "FMA-pipe floor of the kernel's own instruction mix (812 packed + 74 scalar FP instructions per thread and frame, 128 lanes/clk/SM, profiles/r01_microbench_pipe_rates.txt) = 42.8 M frames/s = 0.537 of HBM peak at 20 B/sample"},
-                "note": "75% overlap: 280 flop/sample puts this shape past the FP32 ridge; the binding roof is the FMA pipe, not HBM; see DESIGN.md section 4"}
+                              "note": "FMA-pipe floor of the kernel's own instruction mix (812 packed + 74 scalar FP instructions per thread and frame, 128 lanes/clk/SM) = 42.8 M frames/s at 1965 MHz = 0.537 of HBM peak at 20 B/sample"},
+                "note": "75% overlap: 280 flop/sample puts this shape past the FP32 ridge; see DESIGN.md section 4"}
 
     # ---- end to end through the host API: pinned host in, bands + detector records out ----
     h_iq = PinnedArray((2 * S,), np.int16)
-    h_iq.array[:] = d_iq.cpu().numpy()
+    h_iq.array[:] = d_iq[0].cpu().numpy()
     h_rows = PinnedArray((F, wf.row_width), np.float32)
     h_det = PinnedArray((F,), DET_DTYPE)
     wf.set_stream(None)
+    # the ceiling of this leg: every rank copying its pinned shard to its GPU at the same time
+    h2d_gbs = None
+    try:
+        d_tmp = torch.empty(2 * S, dtype=torch.int16, device=dev)
+        h_t = torch.from_numpy(h_iq.array)
+        d_tmp.copy_(h_t, non_blocking=True)
+        torch.cuda.synchronize()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(4):
+            d_tmp.copy_(h_t, non_blocking=True)
+        torch.cuda.synchronize()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        h2d_gbs = 4 * 4 * S / dt / 1e9
+        del d_tmp
+    except Exception:                               # noqa: BLE001
+        h2d_gbs = None
     e2e_steps = max(3, min(args.steps, 10))
     for _ in range(2):
         wf.process_host(h_iq.array, h_rows.array, h_det.array)
@@ -429,13 +625,64 @@ def main():
     e2e_value = world * S * e2e_steps / dt / 1e6
     checksum = float(h_rows.array[:, 0].sum()) + float(h_det.array["avg"].sum())
     e2e = {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": 4 * used_samples,
-           "d2h_bytes_per_step": F * (4 * wf.row_width + 16), "steps": e2e_steps,
-           "output": "recorder band rows (%d bins) + detector records" % wf.row_width, "checksum": checksum}
+           "d2h_bytes_per_step": F * (4 * wf.row_width + 16), "steps": e2e_steps, "samples_per_step": S,
+           "output": "recorder band rows (%d bins) + detector records" % wf.row_width, "checksum": checksum,
+           "h2d_gbs_per_gpu_concurrent": h2d_gbs,
+           "h2d_ceiling_msamples_per_s": (world * h2d_gbs * 1e9 / 4 / 1e6) if h2d_gbs else None,
+           "placement": placement}
 
-    cpu_baseline = None
-    dropin = None
+    cpu_baseline = cpu_alt = dropin = parity = fp64 = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        # 30 min of station data: about 11 s of work for the reference on one core
+        # ---- parity of the timed input: its first frames against the oracle (the checker), the tests' rule
+        # and the strict one of BASELINE.md section 5 ----
+        try:
+            from oracle import ref_numpy as R
+            nfr = 48
+            ns = BINS + (nfr - 1) * HOP
+            iq_head = h_iq.array[:2 * ns].copy()
+            wfp = ro.Waterfall(BINS, OVERLAP, sample_rate=SR, in_format=ro.IN_INT16, device=local_rank)
+            rows_gpu, _, _ = wfp.process_host(iq_head)
+            wfp.close()
+            ref = R.waterfall_rows(iq_head, BINS, OVERLAP).astype(np.float64)
+            g64 = rows_gpu.astype(np.float64)
+            err = np.abs(g64 - ref)
+            tol = np.maximum((10.0 ** (1e-3 / 20.0) - 1.0) * np.abs(ref), 2.0 ** -22 * np.abs(ref).max(axis=1, keepdims=True))
+            rms = np.sqrt(np.mean(ref * ref, axis=1, keepdims=True))
+            strict = np.maximum(5e-6 * np.abs(ref), 1e-6 * rms)
+            parity = {"rule": "per bin |gpu - ref| <= max(1e-3 dB x |ref|, 2^-22 x max|row|) (tests/helpers.py); "
+                              "strict = 5e-6 relative or 1e-6 x RMS(row) (BASELINE.md section 5)",
+                      "frames": nfr, "worst_err_over_tol": float((err / tol).max()),
+                      "frac_bins_strict_5e-6": float((err <= strict).mean()),
+                      "worst_err_over_strict": float((err / strict).max()), "precision": "fp32"}
+            wf64 = ro.Waterfall(BINS, OVERLAP, sample_rate=SR, in_format=ro.IN_INT16, device=local_rank, precision=ro.PREC_FP64)
+            rows64, _, _ = wf64.process_host(iq_head)
+            e64 = np.abs(rows64.astype(np.float64) - ref)
+            parity["fp64"] = {"worst_err_over_strict": float((e64 / strict).max()),
+                              "frac_bins_strict_5e-6": float((e64 <= strict).mean()),
+                              "frac_bins_bit_identical": float((rows64 == ref.astype(np.float32)).mean())}
+            # ---- throughput of the FP64 variant on a smaller shard (multi-kernel, a global scratch) ----
+            S64 = 1 << 24
+            F64 = wf64.frame_count(S64)
+            wf64.set_stream(stream.cuda_stream)
+            for _ in range(2):
+                wf64.process_resident(d_iq[0].data_ptr(), S64, d_rows.data_ptr(), None, sync=False)
+            torch.cuda.synchronize()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record(stream)
+            for _ in range(5):
+                wf64.process_resident(d_iq[0].data_ptr(), S64, d_rows.data_ptr(), None, sync=False)
+            a1.record(stream)
+            torch.cuda.synchronize()
+            ms64 = a0.elapsed_time(a1) / 5
+            b64 = 4 * ((F64 - 1) * HOP + BINS) + 4 * BINS * F64
+            fp64 = {"value": S64 / (ms64 * 1e-3) / 1e6, "unit": "Msamples/s", "ms_per_shard": ms64, "samples": S64,
+                    "roofline_frac": b64 / (ms64 * 1e-3) / 1e9 / peak, "dtype": "f64",
+                    "what": "cfg.precision = 1 (wf64_* kernels): the variant that meets the strict tolerance on every bin"}
+            wf64.close()
+        except Exception as e:                      # noqa: BLE001
+            parity = {"error": "%s: %s" % (type(e).__name__, e)}
+
+        # ---- CPU baselines: 30 min of station data, about 12 s of work for the reference on one core ----
         secs = 1800.0
         from radio_observer_b200 import synth
         base = "/dev/shm" if os.path.isdir("/dev/shm") else None
@@ -447,52 +694,112 @@ def main():
                 n -= n % 1024
                 wav = os.path.join(wtmp, "in.wav")
                 synth.write_wav(wav, host_station_iq(n, 0x5EED0002), SR)
-            v, kind, cores, desc = run_reference_cpu(secs, 1, wav_path=wav)
-            cpu_baseline = {"value": v, "unit": "Msamples/s", "cores": cores, "kind": kind, "sample": desc}
+                r = run_reference_cpu(secs, 1, wav_path=wav)
+                cpu_baseline = {"value": r[0], "unit": "Msamples/s", "cores": 1, "kind": "reference",
+                                "sample": "one process, %.0f s of 96 kHz station I/Q (WAV in tmpfs) through the reference's own "
+                                          "Pipeline/WAVStream/WaterfallBackend/BolidRecorder (oracle/_ref, -O2), FITS to tmpfs. %s"
+                                          % (n / SR, FFT_NOTE)}
+            else:
+                v = numpy_port_baseline(20.0)
+                cpu_baseline = {"value": v, "unit": "Msamples/s", "cores": 1, "kind": "port",
+                                "sample": "20 s of station I/Q through oracle/ref_numpy.py (numpy pocketfft)"}
+            # the same path on scipy.fft, the as-shipped -O0 build, and what FFT library the box has
+            cpu_alt = {"fft_probe": fft_probe()}
+            try:
+                iq120 = host_station_iq(120 * SR, 0x5EED0002)
+                nproc = os.cpu_count() or 1
+                t1, fr = scipy_path(iq120, BINS, OVERLAP, det, 1)
+                tn, _ = scipy_path(iq120, BINS, OVERLAP, det, nproc)
+                cpu_alt["scipy_fft"] = {"workers_1": 120 * SR / t1 / 1e6, "workers_all": 120 * SR / tn / 1e6, "cores": nproc,
+                                        "unit": "Msamples/s", "sample": "120 s of station I/Q, framing + window + scipy.fft (pocketfft, "
+                                        "complex128) + magnitude + shift + detector statistics in numpy, %d frames" % fr}
+            except Exception as e:                  # noqa: BLE001
+                cpu_alt["scipy_fft"] = {"error": str(e)}
+            if os.path.exists(REF_BIN_O0):
+                r0 = run_reference_cpu(300.0, 1, binary=REF_BIN_O0)
+                if r0:
+                    cpu_alt["reference_O0"] = {"value": r0[0], "unit": "Msamples/s", "cores": 1,
+                                               "sample": "the same binary built with the reference's shipped flags (-O0 -ggdb, Makefile:26-30), 300 s of station I/Q"}
             # the same WAV through the reference's own Pipeline with one string changed in the config
-            # ("factory": "waterfall_cuda"): what a station operator gets today.  The reference's host side
-            # (WAVStream -> vector<Complex>, one raw-ring push per sample, recorders, FITS) is unchanged and
-            # bounds this number; process start-up and CUDA initialisation (about 1.3 s) are inside it.
+            # ("factory": "waterfall_cuda"): what a station operator gets.  Process start-up and CUDA
+            # initialisation (about 1.3 s) are inside every figure; each variant runs twice.
             wf.close()
-            # Every drop-in figure is one whole process run (6 s or less), so one descheduled thread shows:
-            # each variant runs twice, the better run is the value and both are listed.
-            def best_of_two(**kw):
-                rs = [run_reference_cpu(secs, 1, binary=CUDA_BIN, factory="waterfall_cuda",
-                                        extra={"cuda_batch_frames": 64}, wav_path=wav, **kw) for _ in range(2)]
-                rs = [x for x in rs if x is not None]
-                if not rs:
-                    return None, []
-                return max(rs, key=lambda x: x[0]), [round(x[0], 2) for x in rs]
-            r, runs = best_of_two() if wav else (None, [])
-            if r is not None:
-                dropin = {"value": r[0], "unit": "Msamples/s", "cores": 1, "runs": runs,
-                          "what": "reference Pipeline/WAVStream/recorders unmodified, backend factory waterfall_cuda "
-                                  "(cuda_batch_frames 64), same %.0f s WAV and outputs as cpu_baseline" % secs}
-            # the same again with the narrow-ingest frontend: NarrowWAVStream hands the int16
-            # blocks of the file to CudaWaterfallBackend::processRaw, 4 B per sample from the file to the GPU
-            r, runs = best_of_two(flags=("-N",)) if wav else (None, [])
-            if r is not None and dropin is not None:
-                dropin["narrow_ingest"] = {
-                    "value": r[0], "unit": "Msamples/s", "cores": 1, "runs": runs,
-                    "what": "as above with the frontend NarrowWAVStream -> processRaw(int16) instead of WAVStream -> "
-                            "process(vector<Complex>); recorders, FITS and CSV output unchanged"}
+            if wav and os.path.exists(CUDA_BIN):
+                def variant(**kw):
+                    r = run_reference_cpu(secs, 1, runs=2, binary=CUDA_BIN, factory="waterfall_cuda", wav_path=wav, **kw)
+                    return None if r is None else {"value": r[0], "unit": "Msamples/s", "cores": 1, "runs": r[1], "startup_crashes": r[3]}
+                dropin = variant(flags=("-N",))
+                if dropin:
+                    dropin["what"] = ("reference Pipeline / recorders / FITSWriter / CsvLog, backend factory waterfall_cuda (bands + "
+                                      "detector records from the GPU), frontend NarrowWAVStream (-N), same %.0f s WAV and outputs as cpu_baseline" % secs)
+                    dropin["vs_cpu_baseline"] = dropin["value"] / cpu_baseline["value"]
+                    w = variant()
+                    if w:
+                        w["what"] = "as above behind the reference's own WAVStream (vector<Complex> blocks, 16 B per sample)"
+                        dropin["wavstream_frontend"] = w
+                    f = variant(flags=("-N",), extra={"cuda_rows": "full"})
+                    if f:
+                        f["what"] = "cuda_rows = full: whole rows back to the host, statistics recomputed by the reference's BolidRecorder (round 1's adapter)"
+                        dropin["full_rows_mode"] = f
         finally:
             shutil.rmtree(wtmp, ignore_errors=True)
 
     if rank == 0:
-        line = {"metric": "complex Msamples/s through waterfall FFT+magnitude+bolid detect",
+        line = {"metric": METRIC,
                 "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "bins": BINS, "overlap": OVERLAP, "sample_rate": SR,
-                           "samples_per_gpu_per_step": S, "frames_per_gpu_per_step": F,
-                           "sharding": "time shards, one per GPU, overlap halo re-read from input; no collective",
-                           "l2": "input %.0f MiB + rows %.0f MiB per step, larger than L2" % (4 * S / 2**20, 4 * BINS * F / 2**20)},
-                "roofline": roofline, "cpu_baseline": cpu_baseline, "dropin": dropin, "e2e": e2e, "clocks": clocks,
+                "config": bench_config(args.log2_samples, P, G),
+                "roofline": roofline, "parity": parity, "fp64": fp64, "cpu_baseline": cpu_baseline,
+                "cpu_baseline_alt": cpu_alt, "dropin": dropin, "e2e": e2e, "clocks": clocks,
+                "timed_region_s": t_wall1 - t_wall0,
                 "gpu_launches": int(launches)}
         emit(line)
     if dist is not None:
         dist.destroy_process_group()
+    return 0
+
+
+def sweep(args, emit, torch, ro, dev):
+    """BASELINE config 5: FFT size 1k..64k x overlap 0/50/75 % on synthetic int16 I/Q, device-resident,
+    with the scipy.fft one-core figure of the same point beside it."""
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    peak = float(json.load(open(peaks_path))["hbm_gbs"]) if os.path.exists(peaks_path) else 6650.0
+    S = 1 << 26
+    rng = np.random.default_rng(5)
+    iq = rng.integers(-3000, 3000, size=2 * S, dtype=np.int16)
+    d_iq = torch.from_numpy(iq).to(dev)
+    d_rows = torch.empty(4 * S + (1 << 20), dtype=torch.float32, device=dev)
+    points = []
+    for lg in range(10, 17):
+        N = 1 << lg
+        _, det = bolidozor_bands(SR, N)
+        for ov in (0, N // 2, 3 * N // 4):
+            wf = ro.Waterfall(N, ov, sample_rate=SR, in_format=ro.IN_INT16)
+            F = wf.frame_count(S)
+            wf.process_resident(d_iq.data_ptr(), S, d_rows.data_ptr(), None, sync=True)
+            wf.set_profiling(True)
+            wf.kernel_times()
+            for _ in range(5):
+                wf.process_resident(d_iq.data_ptr(), S, d_rows.data_ptr(), None, sync=False)
+            ms, n = wf.kernel_times()
+            kname = wf.kernel_name()
+            wf.close()
+            t = ms[0] / max(1, n[0]) * 1e-3
+            hop = N - ov
+            alg = 4 * ((F - 1) * hop + N) + 4 * N * F
+            cpu = None
+            if not args.no_cpu_baseline:
+                nf = max(8, min(64, (1 << 20) // N))
+                tc, fr = scipy_path(iq[:2 * (N + (nf - 1) * hop)], N, ov, det, 1)
+                cpu = fr * hop / tc / 1e6
+            points.append({"bins": N, "overlap": ov, "frames": F, "kernel": kname, "kernel_ms": round(t * 1e3, 4),
+                           "Mframes_per_s": round(F / t / 1e6, 3), "Msamples_per_s": round(F * hop / t / 1e6, 1),
+                           "hbm_frac": round(alg / t / 1e9 / peak, 4), "fft_TFLOPs_5NlogN": round(5.0 * N * lg * F / t / 1e12, 2),
+                           "cpu_scipy_fft_1core_Msamples_per_s": None if cpu is None else round(cpu, 3)})
+            print(json.dumps(points[-1]), file=sys.stderr, flush=True)
+    emit({"metric": "config 5: FFT size x overlap sweep, device-resident, int16 I/Q", "unit": "Msamples/s", "n_gpus": 1,
+          "hbm_peak_gbs": peak, "points": points})
     return 0
 
 

@@ -75,8 +75,15 @@ typedef struct ro_wf_config {
 	 * 1 = FP64 transform and magnitude like the reference's FFTW path (src/FFTBackend.cpp:117-120,
 	 * src/WaterfallBackend.cpp:492-505): rows within 1e-5 relative in linear power on every bin. */
 	int32_t precision;
-	int32_t reserved[3];
+	int32_t tuning;                  /* RO_TUNE_* bits, 0 = the measured defaults                  */
+	int32_t scratch_mb;              /* frames longer than 32768 points: MiB of device scratch per
+	                                    batch of the split path; 0 = 256                            */
+	int32_t reserved[1];
 } ro_wf_config;
+
+/* tuning bits: A/B switches for measurements and tests; results do not depend on them */
+#define RO_TUNE_NO_FUSED   1   /* 32768-point frames through the split path instead of the fused kernel */
+#define RO_TUNE_NO_PAIR    2   /* split path: every residue class stores its own bins (no paired stores) */
 
 /* Per-row detector statistics: what BolidRecorder::update computes before its
  * decision (reference src/BolidRecorder.cpp:121-132, 302-347). */
@@ -137,7 +144,14 @@ size_t ro_wf_row_count(const ro_wf *h, size_t n_samples);
  * Writes FULL rows (ro_wf_out_bins floats each, fftshifted) to d_rows and, if the
  * detector is configured and d_det != NULL, one record per row; max_frames and
  * *n_frames count output rows.  Asynchronous on the handle's stream unless
- * `sync` is non-zero. */
+ * `sync` is non-zero.
+ * Alignment: d_rows 16 bytes (what cudaMalloc returns), float32 d_iq 8 bytes; RO_E_INVALID
+ * otherwise.  int16 d_iq may start anywhere on a sample; frames that start on 16-byte boundaries
+ * (d_iq 16-byte aligned and hop a multiple of 4 samples) take the faster, TMA-staged kernels.
+ * One stream at a time: a handle's work buffers (long-frame scratch, FP64 scratch, reduce scratch)
+ * are shared by all of its calls, so asynchronous calls must all be issued on the SAME stream
+ * (ro_wf_set_stream between two of them needs a ro_wf_sync first), and the batch and streaming
+ * entry points of one handle must not be in flight together. */
 int  ro_wf_process_resident(ro_wf *h, const void *d_iq, size_t n_samples,
                             float *d_rows, ro_det_rec *d_det,
                             size_t max_frames, size_t *n_frames, int sync);
@@ -174,6 +188,8 @@ int  ro_wf_set_profiling(ro_wf *h, int enable);
 int  ro_wf_kernel_times(ro_wf *h, double ms_sum[2], uint64_t launches[2]);
 /* total kernel launches issued by this handle since creation */
 uint64_t ro_wf_launch_count(const ro_wf *h);
+/* which kernel the handle's last transform launch ran (a static string: diagnostics, bench labels) */
+const char *ro_wf_kernel_name(const ro_wf *h);
 
 /* ---- device memory helpers (so callers need no CUDA binding) -------------- */
 int  ro_dev_count(int *n);

@@ -8,6 +8,7 @@ libro_cuda.so and a B200.
 from .capi import (  # noqa: F401
     RoError, WfConfig, DetRec, Waterfall, load_library, library_path,
     window_table, twiddle_table, IN_INT16, IN_FLOAT32, IN_COMPLEX64, PREC_FP32, PREC_FP64,
+    TUNE_NO_FUSED, TUNE_NO_PAIR,
 )
 
 from . import archive  # noqa: F401,E402  (time-sharded archive reprocessing, host-side trigger state machine)
@@ -17,4 +18,5 @@ __all__ = [
     "archive", "fits", "recorders",
     "RoError", "WfConfig", "DetRec", "Waterfall", "load_library", "library_path",
     "window_table", "twiddle_table", "IN_INT16", "IN_FLOAT32", "IN_COMPLEX64", "PREC_FP32", "PREC_FP64",
+    "TUNE_NO_FUSED", "TUNE_NO_PAIR",
 ]

@@ -13,6 +13,7 @@ from typing import Optional, Sequence, Tuple
 import numpy as np
 
 PREC_FP32, PREC_FP64 = 0, 1
+TUNE_NO_FUSED, TUNE_NO_PAIR = 1, 2
 IN_INT16, IN_FLOAT32, IN_COMPLEX64 = 0, 1, 2
 MAX_BANDS = 4
 
@@ -31,7 +32,7 @@ class WfConfig(C.Structure):
         ("det_lo", C.c_int32), ("det_w", C.c_int32), ("noise_lo", C.c_int32), ("noise_w", C.c_int32),
         ("avg_bins", C.c_int32), ("device", C.c_int32), ("max_batch_frames", C.c_int32),
         ("row_avg", C.c_int32), ("bin_decim", C.c_int32), ("precision", C.c_int32),
-        ("reserved", C.c_int32 * 3),
+        ("tuning", C.c_int32), ("scratch_mb", C.c_int32), ("reserved", C.c_int32 * 1),
     ]
 
 
@@ -78,6 +79,7 @@ def load_library():
         "ro_wf_set_stream": (C.c_int, [vp, vp]),
         "ro_wf_sync": (C.c_int, [vp]),
         "ro_wf_set_profiling": (C.c_int, [vp, C.c_int]),
+        "ro_wf_kernel_name": (C.c_char_p, [vp]),
         "ro_wf_kernel_times": (C.c_int, [vp, P(C.c_double), P(u64)]),
         "ro_wf_launch_count": (u64, [vp]),
         "ro_dev_count": (C.c_int, [P(C.c_int)]),
@@ -185,7 +187,7 @@ class Waterfall:
                  iq_gain: float = 0.0, iq_phase_shift: int = 0,
                  bands: Sequence[Tuple[int, int]] = (), detector: Optional[dict] = None,
                  device: int = 0, max_batch_frames: int = 0, row_avg: int = 1, bin_decim: int = 1,
-                 precision: int = 0):
+                 precision: int = 0, tuning: int = 0, scratch_mb: int = 0):
         self.lib = load_library()
         cfg = WfConfig()
         cfg.bins, cfg.overlap, cfg.sample_rate, cfg.in_format = bins, overlap, sample_rate, in_format
@@ -199,6 +201,7 @@ class Waterfall:
             cfg.avg_bins = detector["avg_bins"]
         cfg.device, cfg.max_batch_frames = device, max_batch_frames
         cfg.row_avg, cfg.bin_decim, cfg.precision = row_avg, bin_decim, precision
+        cfg.tuning, cfg.scratch_mb = tuning, scratch_mb
         self.cfg = cfg
         h = C.c_void_p()
         _check(self.lib.ro_wf_create(C.byref(cfg), C.byref(h)))
@@ -321,3 +324,7 @@ class Waterfall:
 
     def launch_count(self) -> int:
         return int(self.lib.ro_wf_launch_count(self.h))
+
+    def kernel_name(self) -> str:
+        """What the last transform launch of this handle ran."""
+        return self.lib.ro_wf_kernel_name(self.h).decode()

@@ -41,43 +41,7 @@ int fail(int code, const char *fmt, ...)
 			            cudaGetErrorString(e_), __FILE__, __LINE__);          \
 	} while (0)
 
-typedef void (*fft_kernel_t)(const ro::WfParams);
 typedef void (*det_kernel_t)(const ro::DetParams);
-
-struct KernelChoice {
-	fft_kernel_t fn;
-	int threads;
-	size_t smem;
-	int log2nb;
-};
-
-template <int LOG2NB, int P, int R3, int MINB, bool PRE>
-KernelChoice pick(int fmt)
-{
-	KernelChoice k;
-	constexpr int NB = 1 << LOG2NB;
-	constexpr int PAD1 = (R3 < 16) ? R3 : 0;
-	k.threads = NB / P;
-	k.smem = sizeof(float2) * (size_t)(NB + P * PAD1);
-	k.log2nb = LOG2NB;
-	if (fmt == ro::FMT_INT16) k.fn = ro::wf_fft_kernel<LOG2NB, P, R3, ro::FMT_INT16, PRE, MINB>;
-	else k.fn = ro::wf_fft_kernel<LOG2NB, P, R3, ro::FMT_FLOAT32, PRE, MINB>;
-	return k;
-}
-
-bool choose_kernel(int log2n, int fmt, KernelChoice *out)
-{
-	switch (log2n) {
-	case 10: *out = pick<10, 16, 4, 12, false>(fmt); return true;
-	case 11: *out = pick<11, 16, 8, 6, false>(fmt); return true;
-	case 12: *out = pick<12, 16, 16, 3, false>(fmt); return true;
-	case 13: *out = pick<13, 32, 8, 2, false>(fmt); return true;
-	case 14: *out = pick<14, 32, 16, 1, false>(fmt); return true;
-	default:
-		if (log2n > 14 && log2n <= 19) { *out = pick<14, 32, 16, 1, true>(fmt); return true; }
-		return false;
-	}
-}
 
 struct Pending {            // one submitted batch of the streaming path
 	uint64_t first_row;
@@ -111,9 +75,9 @@ struct ro_wf {
 	double2 *d_tw64;                      // N/2 entries exp(-2*pi*i*j/N)
 	double2 *d_x64;                       // [x64_frames][N]
 	long long x64_frames;
-	KernelChoice kc;
-	int grid_cap;                         // resident CTAs for the persistent grid
 	det_kernel_t det_fn;
+	const char *last_kernel;              // what launch_fft ran last (ro_wf_kernel_name)
+	char name_staged[96], name_direct[96], name_f32[96];
 	// v2 kernels (int16 input, N = 4096..16384, symmetric window): [0] direct loads, [1] TMA-staged ring
 	bool v2_ok;
 	bool v2_f32;                          // ... or, for float32 input, MODE_DIRECT_F32 in both slots
@@ -317,6 +281,7 @@ int launch_fft(ro_wf *h, cudaStream_t s, const void *d_iq, float *d_rows, long l
 {
 	if (n_frames <= 0) return RO_OK;
 	if (h->fp64) {
+		h->last_kernel = "wf64_load/block/stage/mag_kernel (FP64 variant)";
 		cudaEvent_t e0 = 0, e1 = 0;
 		if (h->profiling) {
 			int rc = get_event(h, &e0); if (rc) return rc;
@@ -356,9 +321,16 @@ int launch_fft(ro_wf *h, cudaStream_t s, const void *d_iq, float *d_rows, long l
 		}
 		return RO_OK;
 	}
+	// every FP32 kernel stores 2 or 4 adjacent magnitudes with one vector store and reads float32 pairs
+	// with 64-bit loads (ro_cuda.h states the contract)
+	if (((uintptr_t)d_rows & 15) != 0 || (row_stride & 3) != 0)
+		return fail(RO_E_INVALID, "device rows must be 16-byte aligned with a pitch that is a multiple of 4 floats");
+	if (h->fmt == ro::FMT_FLOAT32 && ((uintptr_t)d_iq & 7) != 0)
+		return fail(RO_E_INVALID, "float32 device input must be 8-byte aligned");
 	// the fused long-frame kernel stages samples with cp.async.bulk: 16-byte aligned frame starts
-	if (h->fused_ok && ((uintptr_t)d_rows & 15) == 0 && (row_stride & 3) == 0 &&
-	    ((uintptr_t)d_iq & 15) == 0 && ((long long)h->hop * h->in_bytes) % 16 == 0) {
+	if (h->fused_ok && ((uintptr_t)d_iq & 15) == 0 && ((long long)h->hop * h->in_bytes) % 16 == 0) {
+		h->last_kernel = h->fmt == ro::FMT_FLOAT32 ? "wf_fft2_kernel<14,32,16,MODE_FUSED1_F32> (2 x 16k per frame, TMA-staged load phase)"
+		                                           : "wf_fft2_kernel<14,32,16,MODE_FUSED1> (2 x 16k per frame, TMA-staged load phase)";
 		const long long cap = h->v2f_grid_cap;
 		const long long fpc = (n_frames + cap - 1) / cap;          // contiguous frames per CTA
 		const int grid = (int)((n_frames + fpc - 1) / fpc);
@@ -378,6 +350,7 @@ int launch_fft(ro_wf *h, cudaStream_t s, const void *d_iq, float *d_rows, long l
 		return RO_OK;
 	}
 	if (h->split_ok) {
+		h->last_kernel = "wf_split_kernel + wf_fft2_kernel<MODE_SPLIT> (radix-Na step through a scratch, then Na transforms per frame)";
 		cudaEvent_t e0 = 0, e1 = 0;
 		if (h->profiling) {
 			int rc = get_event(h, &e0); if (rc) return rc;
@@ -391,7 +364,7 @@ int launch_fft(ro_wf *h, cudaStream_t s, const void *d_iq, float *d_rows, long l
 			const long long items = nf << h->log2na;
 			const long long cap = h->v2s_grid_cap;
 			long long ipc = (items + cap - 1) / cap;                 // contiguous items per CTA
-			const int pair = (((uintptr_t)d_rows & 15) == 0 && (row_stride & 3) == 0 && !getenv("RO_SPLIT_NOPAIR")) ? 1 : 0;
+			const int pair = (h->cfg.tuning & RO_TUNE_NO_PAIR) ? 0 : 1;
 			if (pair) ipc += ipc & 1;                                // classes r, r+1 stay in one CTA
 			const int grid = (int)((items + ipc - 1) / ipc);
 			CU(ro::v2_launch(h->v2s, grid, s, h->d_scratch, NULL, h->d_tw_nb, d_rows + f0 * row_stride, row_stride,
@@ -404,10 +377,10 @@ int launch_fft(ro_wf *h, cudaStream_t s, const void *d_iq, float *d_rows, long l
 		}
 		return RO_OK;
 	}
-	// v2 stores 2 or 4 adjacent magnitudes with one vector store: rows must be 16-byte aligned
-	if (h->v2_ok && ((uintptr_t)d_rows & 15) == 0 && (row_stride & 3) == 0 && (!h->v2_f32 || ((uintptr_t)d_iq & 7) == 0)) {
+	if (h->v2_ok) {
 		// the staged variant needs 16-byte aligned frame starts for cp.async.bulk
 		const int st = (h->hop % 4 == 0 && ((uintptr_t)d_iq & 15) == 0) ? 1 : 0;
+		h->last_kernel = h->v2_f32 ? h->name_f32 : st ? h->name_staged : h->name_direct;
 		const long long cap = h->v2_grid_cap[st];
 		const long long fpc = (n_frames + cap - 1) / cap;          // contiguous frames per CTA
 		const int grid = (int)((n_frames + fpc - 1) / fpc);
@@ -426,33 +399,7 @@ int launch_fft(ro_wf *h, cudaStream_t s, const void *d_iq, float *d_rows, long l
 		}
 		return RO_OK;
 	}
-	ro::WfParams p;
-	p.iq = d_iq;
-	p.window = h->d_window;
-	p.tw = h->d_tw;
-	p.rows = d_rows;
-	p.n_frames = n_frames;
-	p.hop = h->hop;
-	p.row_stride = row_stride;
-	p.iq_gain = (float)h->cfg.iq_gain;
-	p.log2n = h->log2n;
-	p.log2na = h->log2n - h->kc.log2nb;
-	const long long items = n_frames << p.log2na;
-	const int grid = (int)std::min<long long>(items, h->grid_cap);
-	cudaEvent_t e0 = 0, e1 = 0;
-	if (h->profiling) {
-		int rc = get_event(h, &e0); if (rc) return rc;
-		rc = get_event(h, &e1); if (rc) return rc;
-		CU(cudaEventRecord(e0, s));
-	}
-	h->kc.fn<<<grid, h->kc.threads, h->kc.smem, s>>>(p);
-	CU(cudaGetLastError());
-	h->launches++;
-	if (h->profiling) {
-		CU(cudaEventRecord(e1, s));
-		h->ev_used[0].push_back(std::make_pair(e0, e1));
-	}
-	return RO_OK;
+	return fail(RO_E_STATE, "no kernel for bins = %d on this handle", h->N);
 }
 
 int launch_detect(ro_wf *h, cudaStream_t s, const float *d_rows, long long row_stride,
@@ -608,18 +555,15 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 	h->out_bins = NO;
 	h->row_width = cfg->n_bands ? width : NO;
 	h->det_on = det_on;
-	if (!choose_kernel(h->log2n, h->fmt, &h->kc)) { free_all(h); return fail(RO_E_INVALID, "no kernel for bins = %d", N); }
-
 	cudaDeviceProp prop;
 	cudaError_t e = cudaGetDeviceProperties(&prop, cfg->device);
 	if (e != cudaSuccess) { free_all(h); return fail(RO_E_CUDA, "cudaGetDeviceProperties: %s", cudaGetErrorString(e)); }
 	h->n_sms = prop.multiProcessorCount;
-	e = cudaFuncSetAttribute((const void *)h->kc.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->kc.smem);
-	if (e != cudaSuccess) { free_all(h); return fail(RO_E_CUDA, "kernel image unusable on device %d (%s): %s; this library is built for sm_100a only", cfg->device, prop.name, cudaGetErrorString(e)); }
-	int occ = 0;
-	e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void *)h->kc.fn, h->kc.threads, h->kc.smem);
-	if (e != cudaSuccess || occ < 1) { free_all(h); return fail(RO_E_CUDA, "occupancy query failed: %s", cudaGetErrorString(e)); }
-	h->grid_cap = occ * h->n_sms;
+	if (prop.major != 10) {
+		free_all(h);
+		return fail(RO_E_CUDA, "device %d (%s) is sm_%d%d: this library holds sm_100a code only and has no other path",
+		            cfg->device, prop.name, prop.major, prop.minor);
+	}
 
 	{   // detector variant by noise band width
 		const int epl = (cfg->noise_w + 31) / 32;
@@ -647,8 +591,7 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 	{   // v2 eligibility: an instantiated size and a symmetric window
 		const bool gain = cfg->iq_gain != 0.0;
 		h->v2_ok = false;
-		const char *force_v1 = getenv("RO_FORCE_V1");
-		if (sym && h->fmt == ro::FMT_INT16 && !(force_v1 && force_v1[0] == '1') &&
+		if (sym && h->fmt == ro::FMT_INT16 &&
 		    ro::v2_pick(h->log2n, ro::V2_DIRECT, gain, &h->v2[0]) && ro::v2_pick(h->log2n, ro::V2_STAGED, gain, &h->v2[1])) {
 			h->v2_ok = true;
 			for (int st = 0; st < 2; st++) {
@@ -660,10 +603,9 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 			}
 		}
 		// float32 input (raw TCP / JACK / the adapter's narrowed Complex): the same kernel reading packed
-		// float pairs from global memory; both slots hold it, the launcher's alignment test picks either
+		// float pairs from global memory; both slots hold it
 		h->v2_f32 = false;
-		if (sym && h->fmt == ro::FMT_FLOAT32 && !(force_v1 && force_v1[0] == '1') && !getenv("RO_NO_V2_F32") &&
-		    ro::v2_pick_f32(h->log2n, gain, &h->v2[0])) {
+		if (sym && h->fmt == ro::FMT_FLOAT32 && ro::v2_pick_f32(h->log2n, gain, &h->v2[0])) {
 			h->v2[1] = h->v2[0];
 			CUH(cudaFuncSetAttribute(h->v2[0].fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->v2[0].smem));
 			int occ2 = 0;
@@ -672,6 +614,12 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 				h->v2_grid_cap[0] = h->v2_grid_cap[1] = occ2 * h->n_sms;
 				h->v2_ok = h->v2_f32 = true;
 			}
+		}
+		if (h->v2_ok) {
+			const int P = h->v2[0].threads ? N / h->v2[0].threads : 0;
+			snprintf(h->name_staged, sizeof h->name_staged, "wf_fft2_kernel<%d,%d,%d,MODE_STAGED%s> (TMA-staged sample ring)", h->log2n, P, N / (P * P), gain ? ",GAIN" : "");
+			snprintf(h->name_direct, sizeof h->name_direct, "wf_fft2_kernel<%d,%d,%d,MODE_DIRECT%s> (unaligned frame starts)", h->log2n, P, N / (P * P), gain ? ",GAIN" : "");
+			snprintf(h->name_f32, sizeof h->name_f32, "wf_fft2_kernel<%d,%d,%d,MODE_DIRECT_F32%s>", h->log2n, P, N / (P * P), gain ? ",GAIN" : "");
 		}
 	}
 	h->fp64 = cfg->precision == RO_PREC_FP64;
@@ -693,16 +641,12 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 	// chaining pass 1 as well (bit 0) costs 5 %: its warps already arrive staggered from pass 3
 	// bit 3: the pass-2 chain releases the warp two levels down (0.7 .. 3.9 % over distance 1)
 	h->stagger = 14;
-	if (const char *e4 = getenv("RO_STAGGER")) h->stagger = atoi(e4);
 	// 8k kernel (two 256-thread CTAs per SM): chaining passes 2 and 3 gives 43.5 -> 47.2 M frames/s;
 	// the 4k kernel (three CTAs per SM) gains nothing
 	h->stagger_small = h->log2n == 13 ? 6 : 0;
-	if (const char *e5 = getenv("RO_STAGGER_SMALL")) h->stagger_small = atoi(e5);
 	int log2nb = 14;                              // in-CTA transform of the split path
-	if (const char *e3 = getenv("RO_SPLIT_LOG2NB")) log2nb = atoi(e3);
 	if (h->log2n - log2nb > 5) log2nb = h->log2n - 5;      // the split kernel does radix <= 32
-	if (h->log2n > 14 && !(getenv("RO_FORCE_V1") && getenv("RO_FORCE_V1")[0] == '1') &&
-	    ro::v2_pick(log2nb, ro::V2_SPLIT, false, &h->v2s)) {
+	if (h->log2n > 14 && ro::v2_pick(log2nb, ro::V2_SPLIT, false, &h->v2s)) {
 		h->log2na = h->log2n - log2nb;
 		const int NBv = 1 << log2nb;
 		CUH(cudaFuncSetAttribute(h->v2s.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->v2s.smem));
@@ -717,25 +661,26 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 			// a batch = whole waves of the persistent grid.  Measured on B200 (32k/64k frames): a 40 MB
 			// scratch that stays in the 126 MB L2 gives only 2 items per CTA per launch and loses more to
 			// launch gaps and tails than a 256 MB scratch loses to HBM (3.9 vs 4.5 M frames/s at 32k);
-			// RO_SCRATCH_MB overrides
+			// cfg.scratch_mb overrides
 			const long long na = 1LL << h->log2na;
 			long long unit = h->v2s_grid_cap, a = unit, b = na;     // frames per wave = cap / gcd(cap, Na)
 			while (b) { long long t2 = a % b; a = b; b = t2; }
 			unit /= a;
 			long long budget_mb = 256;
-			if (const char *e2 = getenv("RO_SCRATCH_MB")) budget_mb = atoll(e2) > 0 ? atoll(e2) : budget_mb;
+			if (cfg->scratch_mb > 0) budget_mb = cfg->scratch_mb;
 			const long long frame_bytes = 8LL * N;
 			long long units = (budget_mb << 20) / (unit * frame_bytes);
 			if (units < 1) units = 1;
-			h->scratch_frames = units * unit;
+			// the split kernel indexes frames with blockIdx.y: at most 65535 per launch
+			if (units * unit > 65535) units = std::max<long long>(1, 65535 / unit);
+			h->scratch_frames = std::min<long long>(units * unit, 65535);
 			CUH(cudaMalloc(&h->d_scratch, (size_t)(h->scratch_frames * frame_bytes)));
 			h->split_ok = true;
 		}
 	}
 	h->fused_ok = false;
-	if (h->split_ok && sym && log2nb == 14 && h->log2na == 1 && !getenv("RO_NO_FUSED") &&
-	    (h->fmt == ro::FMT_INT16 ? ro::v2_pick(14, ro::V2_FUSED1, false, &h->v2f)
-	     : h->fmt == ro::FMT_FLOAT32 && !getenv("RO_NO_FUSED_F32") && ro::v2_pick_fused_f32(&h->v2f))) {
+	if (h->split_ok && sym && log2nb == 14 && h->log2na == 1 && !(cfg->tuning & RO_TUNE_NO_FUSED) &&
+	    (h->fmt == ro::FMT_INT16 ? ro::v2_pick(14, ro::V2_FUSED1, false, &h->v2f) : ro::v2_pick_fused_f32(&h->v2f))) {
 		CUH(cudaFuncSetAttribute(h->v2f.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->v2f.smem));
 		int occ4 = 0;
 		CUH(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, h->v2f.fn, h->v2f.threads, h->v2f.smem));
@@ -826,6 +771,13 @@ extern "C" int ro_wf_kernel_times(ro_wf *h, double ms_sum[2], uint64_t launches[
 }
 
 extern "C" uint64_t ro_wf_launch_count(const ro_wf *h) { return h ? h->launches : 0; }
+
+extern "C" const char *ro_wf_kernel_name(const ro_wf *h)
+{
+	if (!h) return "";
+	if (h->last_kernel) return h->last_kernel;
+	return h->fp64 ? "wf64_load/block/stage/mag_kernel (FP64 variant)" : "(nothing launched yet)";
+}
 
 // ---------------------------------------------------------------------------
 // batch paths

@@ -4,7 +4,7 @@
 // (reference src/FFTBackend.cpp:117-120,236).  Here the transform is a
 // three-pass Cooley-Tukey decomposition N = R1*R2*R3 whose passes run
 // entirely in registers (radix 4..32 per thread) and exchange data through
-// shared memory; these helpers are the per-thread pieces.
+// shared memory; the constants and index helpers of the per-thread pieces (ro_fft2.cuh).
 #pragma once
 #include <cuda_runtime.h>
 
@@ -57,85 +57,6 @@ __host__ __device__ constexpr int bitrev(int v, int bits)
 	int r = 0;
 	for (int i = 0; i < bits; i++) r |= ((v >> i) & 1) << (bits - 1 - i);
 	return r;
-}
-
-__device__ __forceinline__ float2 cmul(float2 a, float2 b)
-{
-	return make_float2(fmaf(a.x, b.x, -(a.y * b.y)), fmaf(a.x, b.y, a.y * b.x));
-}
-
-// In-place forward DIF FFT of R points held in registers.  Output k is left
-// at v[bitrev(k)].  All indices are compile-time after unrolling, so v[] never
-// leaves the register file.
-template <int R>
-__device__ __forceinline__ void fft_dif(float2 (&v)[R])
-{
-	static_assert(R >= 2 && R <= 32 && (R & (R - 1)) == 0, "radix");
-	constexpr int L = ilog2(R);
-#pragma unroll
-	for (int lvl = 0; lvl < L; lvl++) {
-		const int half = R >> (lvl + 1);
-#pragma unroll
-		for (int s = 0; s < R; s += 2 * half) {
-#pragma unroll
-			for (int j = 0; j < half; j++) {
-				const float2 a = v[s + j];
-				const float2 b = v[s + j + half];
-				v[s + j] = make_float2(a.x + b.x, a.y + b.y);
-				const float dx = a.x - b.x, dy = a.y - b.y;
-				const int e = j * (16 / half);        // W_{2*half}^j = W_32^e
-				if (e == 0) {
-					v[s + j + half] = make_float2(dx, dy);
-				} else if (e == 8) {                  // * (-i)
-					v[s + j + half] = make_float2(dy, -dx);
-				} else {
-					const float wr = cw32(e), wi = -sw32(e);
-					v[s + j + half] = make_float2(fmaf(dx, wr, -(dy * wi)),
-					                              fmaf(dx, wi, dy * wr));
-				}
-			}
-		}
-	}
-}
-
-// Multiply output k (at v[bitrev(k)]) by w^k, k = 1..R-1, where
-// base[i] = w^(2^i) were read from an accurately rounded table.  Powers are
-// composed as w^(hi) * w^(lo) with at most ilog2(R)-1 chained products.
-template <int R>
-__device__ __forceinline__ void twiddle_powers(float2 (&v)[R], const float2 (&base)[ilog2(R)])
-{
-	constexpr int L = ilog2(R);
-	constexpr int LB = (L + 1) / 2;       // low bits
-	constexpr int NLO = 1 << LB;
-	constexpr int NHI = 1 << (L - LB);
-	float2 lo[NLO];
-	lo[0] = make_float2(1.f, 0.f);
-#pragma unroll
-	for (int msb = 0; msb < LB; msb++) {
-		lo[1 << msb] = base[msb];
-#pragma unroll
-		for (int rest = 1; rest < (1 << msb); rest++)
-			lo[(1 << msb) + rest] = cmul(base[msb], lo[rest]);
-	}
-	float2 hi[NHI];
-	hi[0] = make_float2(1.f, 0.f);
-#pragma unroll
-	for (int msb = 0; msb < L - LB; msb++) {
-		hi[1 << msb] = base[LB + msb];
-#pragma unroll
-		for (int rest = 1; rest < (1 << msb); rest++)
-			hi[(1 << msb) + rest] = cmul(base[LB + msb], hi[rest]);
-	}
-#pragma unroll
-	for (int h = 0; h < NHI; h++) {
-#pragma unroll
-		for (int j = 0; j < NLO; j++) {
-			const int k = h * NLO + j;
-			if (k == 0) continue;
-			const float2 w = h == 0 ? lo[j] : (j == 0 ? hi[h] : cmul(hi[h], lo[j]));
-			v[bitrev(k, L)] = cmul(v[bitrev(k, L)], w);
-		}
-	}
 }
 
 __device__ __forceinline__ float fast_sqrt(float x)

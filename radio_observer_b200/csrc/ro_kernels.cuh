@@ -1,170 +1,17 @@
-// ro_kernels.cuh -- the fused waterfall kernel and the detector kernel (sm_100a).
+// ro_kernels.cuh -- the kernels that follow the transform (sm_100a).
 //
-// wf_fft_kernel fuses, per frame, what the reference does in
-//   FFTBackend::process        (src/FFTBackend.cpp:211-247: framing, IQ gain, window)
-//   fftw_execute               (src/FFTBackend.cpp:236: N-point forward DFT)
-//   WaterfallBackend::processFFT (src/WaterfallBackend.cpp:492-505: magnitude, fftshift)
 // wf_detect_kernel computes BolidRecorder's per-row statistics
-//   (src/BolidRecorder.cpp:121-132, 302-347).
+//   (src/BolidRecorder.cpp:121-132, 302-347);
+// wf_reduce_kernel is the optional row-average / bin-decimate stage (no reference counterpart).
+// The transform itself is wf_fft2_kernel (ro_kernels2.cuh).
 #pragma once
 #include <stdint.h>
 #include "ro_fft.cuh"
 
 namespace ro {
 
-struct WfParams {
-	const void   *iq;        // device input, interleaved I/Q (int16 or float32)
-	const float  *window;    // N floats (Nuttall, host-built)
-	const float2 *tw;        // N entries exp(-2*pi*i*j/N)
-	float        *rows;      // [n_frames][row_stride] fftshifted magnitudes
-	long long     n_frames;
-	long long     hop;       // samples between frame starts
-	long long     row_stride;
-	float         iq_gain;   // added to Q before the window
-	int           log2n;     // log2(N)
-	int           log2na;    // N = Na * Nb, Nb = the in-CTA transform size
-};
-
 enum { FMT_INT16 = 0, FMT_FLOAT32 = 1 };
 
-template <int FMT>
-__device__ __forceinline__ float2 load_sample(const void *iq, long long idx, float gain)
-{
-	float2 s;
-	if (FMT == FMT_INT16) {
-		const short2 v = __ldg(reinterpret_cast<const short2 *>(iq) + idx);
-		s = make_float2((float)v.x, (float)v.y);
-	} else {
-		s = __ldg(reinterpret_cast<const float2 *>(iq) + idx);
-	}
-	s.y += gain;
-	return s;
-}
-
-// One CTA transforms one (frame, ka) item of Nb = R1*R2*R3 points, P = R1 = R2
-// points per thread, T = Nb/P threads.
-//
-//   n = n1*(R2*R3) + n2*R3 + n3,   k = k1 + R1*k2 + R1*R2*k3
-//   pass 1: DFT over n1, times W_Nb^{(n2*R3+n3)*k1}
-//   pass 2: DFT over n2, times W_{R2*R3}^{n3*k2}
-//   pass 3: DFT over n3, magnitude, store at row index (k + N/2) mod N
-//
-// For N > Nb (log2na > 0) the frame is first split by one radix-Na DIF step
-// folded into the load stage: item (f, ka) transforms
-//   y[s] = W_N^{s*ka} * sum_na xw[na*Nb + s] * W_Na^{na*ka}
-// and its outputs are bins ka + Na*kb.
-template <int LOG2NB, int P, int R3, int FMT, bool PRE, int MINB>
-__global__ void __launch_bounds__((1 << LOG2NB) / P, MINB)
-wf_fft_kernel(const WfParams p)
-{
-	constexpr int NB = 1 << LOG2NB;
-	constexpr int R1 = P, R2 = P;
-	constexpr int T = NB / P;
-	constexpr int M = NB / R1;                 // = R2*R3
-	static_assert(R1 * R2 * R3 == NB, "factorisation");
-	static_assert(R3 <= 16 && R3 >= 2 && P % R3 == 0, "R3");
-	constexpr int PAD1 = (R3 < 16) ? R3 : 0;
-	constexpr int ROW1 = M + PAD1;
-	constexpr int LP = ilog2(P);
-	constexpr int L3 = ilog2(R3);
-	constexpr int SW = 16 / R3;                // exchange-2 swizzle step
-
-	extern __shared__ float2 S[];
-	const int t = threadIdx.x;
-	const int N = 1 << p.log2n;
-	const int NA = 1 << p.log2na;
-	const int nmask = N - 1;
-
-	// per-thread twiddle bases, fixed for the life of the CTA
-	float2 b1[LP], b2[LP];
-	{
-		const int n3 = t % R3;
-		const int step2 = N / M;               // W_{R2*R3} = W_N^{N/M}
-#pragma unroll
-		for (int i = 0; i < LP; i++) {
-			b1[i] = __ldg(p.tw + (((t * NA) << i) & nmask));
-			b2[i] = __ldg(p.tw + (((n3 * step2) << i) & nmask));
-		}
-	}
-
-	const long long items = p.n_frames << p.log2na;
-	for (long long item = blockIdx.x; item < items; item += gridDim.x) {
-		const long long f = item >> p.log2na;
-		const int ka = (int)(item & (NA - 1));
-		const long long base = f * p.hop;
-
-		float2 v[P];
-		// ---- load + window (+ radix-Na pre-step) ----
-		if (!PRE) {
-#pragma unroll
-			for (int n1 = 0; n1 < R1; n1++) {
-				const int s = n1 * M + t;
-				const float2 x = load_sample<FMT>(p.iq, base + s, p.iq_gain);
-				const float w = __ldg(p.window + s);
-				v[n1] = make_float2(x.x * w, x.y * w);
-			}
-		} else {
-#pragma unroll
-			for (int n1 = 0; n1 < R1; n1++) {
-				const int s = n1 * M + t;
-				float2 acc = make_float2(0.f, 0.f);
-				for (int na = 0; na < NA; na++) {
-					const int g = na * NB + s;
-					float2 x = load_sample<FMT>(p.iq, base + g, p.iq_gain);
-					const float w = __ldg(p.window + g);
-					x.x *= w; x.y *= w;
-					const float2 c = __ldg(p.tw + ((((na * ka) & (NA - 1)) << (p.log2n - p.log2na)) & nmask));
-					acc.x += fmaf(x.x, c.x, -(x.y * c.y));
-					acc.y += fmaf(x.x, c.y, x.y * c.x);
-				}
-				const float2 c = __ldg(p.tw + ((s * ka) & nmask));
-				v[n1] = cmul(acc, c);
-			}
-		}
-
-		// ---- pass 1 ----
-		fft_dif<R1>(v);
-		twiddle_powers<R1>(v, b1);
-#pragma unroll
-		for (int k1 = 0; k1 < R1; k1++) S[k1 * ROW1 + t] = v[bitrev(k1, LP)];
-		__syncthreads();
-
-		// ---- pass 2 ----
-		{
-			const int k1 = t / R3, n3 = t % R3;
-#pragma unroll
-			for (int n2 = 0; n2 < R2; n2++) v[n2] = S[k1 * ROW1 + n2 * R3 + n3];
-			fft_dif<R2>(v);
-			twiddle_powers<R2>(v, b2);
-			__syncthreads();
-			const int col = k1 ^ (n3 * SW);
-#pragma unroll
-			for (int k2 = 0; k2 < R2; k2++) S[(k2 * R3 + n3) * R1 + col] = v[bitrev(k2, LP)];
-		}
-		__syncthreads();
-
-		// ---- pass 3 + magnitude + fftshift store ----
-		float *row = p.rows + f * p.row_stride;
-#pragma unroll
-		for (int c = 0; c < P / R3; c++) {
-			const int pidx = t + c * T;
-			const int k1 = pidx % R1, k2 = pidx / R1;
-			float2 u[R3];
-#pragma unroll
-			for (int n3 = 0; n3 < R3; n3++) u[n3] = S[(k2 * R3 + n3) * R1 + (k1 ^ (n3 * SW))];
-			fft_dif<R3>(u);
-#pragma unroll
-			for (int k3 = 0; k3 < R3; k3++) {
-				const int kb = pidx + k3 * (NB / R3);
-				const int kk = ka + (kb << p.log2na);
-				const int j = (kk + (N >> 1)) & nmask;
-				const float2 z = u[bitrev(k3, L3)];
-				row[j] = fast_sqrt(fmaf(z.x, z.x, z.y * z.y));
-			}
-		}
-		__syncthreads();
-	}
-}
 
 // ---------------------------------------------------------------------------
 // Row reduction (extension, default off): |X|^2, accumulate `row_avg` consecutive

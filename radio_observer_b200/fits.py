@@ -95,6 +95,44 @@ def snapshot_cards(width: int, length: int, *, origin: str, time_sec: int, time_
     return cards
 
 
+def raw_cards(length: int, *, origin: str, time_sec: int, time_usec: int, sample_rate: int,
+              git_version: str = "", local_time: str = "", date: str = "") -> List[str]:
+    """The header of a bolid's raw-I/Q file (SnapshotRecorder::writeRaw, reference
+    src/WaterfallBackend.cpp:214-267): a 2 x length float image, CDELT2 = (float)1000 / (float)sample rate
+    as a float card, CRVAL1 / CDELT1 / CRPIX2 as integers."""
+    ms = int(np.float64(time_sec) * 1000.0 + np.float64(time_usec) / 1000.0)
+    cards = [
+        _card_value("SIMPLE", "T", "file does conform to FITS standard"),
+        _card_value("BITPIX", "-32", "number of bits per data pixel"),
+        _card_value("NAXIS", "2", "number of data axes"),
+        _card_value("NAXIS1", "2", "length of data axis 1"),
+        _card_value("NAXIS2", str(int(length)), "length of data axis 2"),
+        _card_value("EXTEND", "T", "FITS dataset may contain extensions"),
+        _pad80("COMMENT   FITS (Flexible Image Transport System) format is defined in 'Astronomy"),
+        _pad80("COMMENT   and Astrophysics', volume 376, page 359; bibcode: 2001A&A...376..359H"),
+        _pad80("COMMENT File created by %s." % PACKAGE_STRING),
+        _pad80("COMMENT Git version: %s" % git_version),
+        _pad80("COMMENT See %s." % PACKAGE_URL),
+        _card_string("ORIGIN", origin),
+    ]
+    if date:
+        cards.append(_card_string("DATE", date, "file creation date (YYYY-MM-DDThh:mm:ss UT)"))
+    cards += [
+        _pad80("COMMENT Local time: %s" % local_time),
+        _card_string("DATE-OBS", format_time(time_sec, "%Y-%m-%dT%H:%M:%S"), "observation date (UTC)"),
+        _card_string("CTYPE2", "TIME", "in seconds"),
+        _card_value("CRPIX2", "1"),
+        _card_value("CRVAL2", str(ms), "unix time of the first IQ sample in this file in ms"),
+        _card_value("CDELT2", _fmt_real(float(np.float32(np.float32(1000.0) / np.float32(sample_rate))), 7),
+                    "time difference between two IQ samples in ms"),
+        _card_string("CTYPE1", "CHAN", "in Hz"),
+        _card_value("CRPIX1", _fmt_real(1.0, 7)),
+        _card_value("CRVAL1", "0"),
+        _card_value("CDELT1", "1"),
+    ]
+    return cards
+
+
 def file_basename(time_sec: int, time_usec: int, origin: str, typ: str, ext: str = "fits") -> str:
     """SnapshotRecorder::getFileBasename (reference src/WaterfallBackend.cpp:320-336)."""
     return "%s%03d_%s_%s.%s" % (format_time(time_sec, "%Y%m%d%H%M%S"), time_usec // 1000, origin, typ, ext)

@@ -143,3 +143,64 @@ def write_planned(path: str, plan: PlannedFile, band_rows: np.ndarray, *, left_b
                              bin_width=A.bin_to_frequency(1, sample_rate, bins) - A.bin_to_frequency(0, sample_rate, bins),
                              git_version=git_version, local_time=local_time)
     F.write_image(path, cards, px)
+
+
+# ---------------------------------------------------------------------------
+# 8f N3  raw-I/Q file of a bolid (reference src/WaterfallBackend.cpp:35-46, 214-267,
+#        src/WaterfallBackend.h:84-87, src/FFTBackend.cpp:217-251, src/FFTBackend.h:129-132)
+# ---------------------------------------------------------------------------
+RAW_CHUNK_ROWS = (1024 * 1024) // 8          # samples per 1 MiB chunk of the raw ring (float pairs)
+
+
+def raw_ring_capacity(buffer_rows: int, *, sample_rate: int, bins: int, overlap: int) -> int:
+    """Samples the reference's raw I/Q ring holds: WaterfallBackend::fftSamplesToRaw(bufferSize) rounded up
+    to whole chunks (RingBuffer2D::resize)."""
+    fsr = A.fft_sample_rate(sample_rate, bins, A.clamp_overlap(bins, overlap))
+    want = int((float(buffer_rows) / float(fsr)) * float(sample_rate))
+    return -(-want // RAW_CHUNK_ROWS) * RAW_CHUNK_ROWS
+
+
+def raw_extent(plan: PlannedFile, *, sample_rate: int, bins: int, overlap: int, ring_capacity: int) -> Tuple[int, int]:
+    """(first sample, sample count) of the raw-I/Q file that goes with bolid file `plan`.
+
+    start = fftMarkToRaw(snapshot.start) is the raw mark stored in handle slot `start`, i.e. the one of
+    row start - 1 (the slot quirk above): the ring mark after the push of the first sample of the frame
+    that FOLLOWS that row when overlap > 0 (FFTBackend::process shifts its handle table before it calls
+    processFFT), of that row's own first sample when overlap = 0.  A mark points at the NEXT slot, so the
+    file begins one sample later.  A slot never written (start <= 0) holds mark 0.
+    count = Recorder::fftSamplesToRaw(length): the row rate truncated to an integer (Q6).
+    Valid while the ring has not been lapped between detection and writing (it holds 8 snapshot lengths)."""
+    ov = A.clamp_overlap(bins, overlap)
+    hop = bins - ov
+    fsr = A.fft_sample_rate(sample_rate, bins, ov)
+    count = A.fft_samples_to_raw(plan.length, fsr, sample_rate)
+    if plan.start_row <= 0:
+        return 0, count
+    r = plan.start_row - 1
+    s = (r + 1) * hop if ov > 0 else r * hop
+    # the mark is (s + 1) % ring_capacity and that slot receives sample s + 1
+    return s + 1, count
+
+
+def raw_pixels(iq_int16: np.ndarray, first: int, count: int) -> np.ndarray:
+    """[count][2] float32 (I, Q) from interleaved int16 I/Q; samples past the end of the archive read as
+    zeros (the reference reads whatever the ring slot held)."""
+    n = iq_int16.shape[0] // 2
+    out = np.zeros((count, 2), dtype=np.float32)
+    a, b = max(0, first), min(n, first + count)
+    if b > a:
+        out[a - first:b - first] = np.asarray(iq_int16[2 * a:2 * b]).reshape(-1, 2).astype(np.float32)
+    return out
+
+
+def write_raw(path: str, plan: PlannedFile, iq_int16: np.ndarray, *, sample_rate: int, bins: int, overlap: int,
+              ring_capacity: int, origin: str, git_version: str = "", local_time: str = "") -> None:
+    """The `raws` FITS file of a bolid: named like the bolid file with type "raws" (getFileName("raws", "fits", time))."""
+    first, count = raw_extent(plan, sample_rate=sample_rate, bins=bins, overlap=overlap, ring_capacity=ring_capacity)
+    cards = F.raw_cards(count, origin=origin, time_sec=plan.time[0], time_usec=plan.time[1], sample_rate=sample_rate,
+                        git_version=git_version, local_time=local_time)
+    F.write_image(path, cards, raw_pixels(iq_int16, first, count))
+
+
+def raw_file_name(plan: PlannedFile, origin: str) -> str:
+    return F.file_basename(plan.time[0], plan.time[1], origin, "raws")

@@ -122,6 +122,50 @@ def _rank_main(rank, world, port, path, bins, overlap, q):
     dist.destroy_process_group()
 
 
+def _rank_main_shared(rank, world, port, path, bins, overlap, shared, q):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    iq = np.load(path, mmap_mode="r")
+
+    def staged(iq_map, s0, s1, rows_out, det_out):      # the checker in place of staged_compute() on a GPU-less host
+        rows = R.waterfall_rows(np.asarray(iq_map[2 * s0:2 * s1]), bins, overlap).astype(np.float32)
+        rows_out[:] = rows[:, 100:300]
+        return len(rows)
+    staged.row_width = 200
+
+    rows, det, shards = A.reprocess_archive(iq, bins, overlap, rank=rank, world=world, dist=dist, shared_dir=shared, staged=staged)
+    if rank == 0:
+        q.put((np.array(rows), [(s.frame0, s.frame1) for s in shards]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_ranks_write_their_shards_in_place_into_shared_arrays(tmp_path, world):
+    """The archive driver's merge: rank 0 creates the merged arrays as files every rank maps, each rank
+    writes its own frame range, two barriers, nothing gathered."""
+    import torch.multiprocessing as mp
+    bins, overlap = 1024, 512
+    rng = np.random.default_rng(12)
+    iq = rng.integers(-3000, 3000, size=2 * 30000, dtype=np.int16)
+    path = str(tmp_path / "iq.npy")
+    np.save(path, iq)
+    whole = R.waterfall_rows(iq, bins, overlap).astype(np.float32)[:, 100:300]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + (os.getpid() % 2000) + world
+    procs = [ctx.Process(target=_rank_main_shared, args=(r, world, port, path, bins, overlap, str(tmp_path), q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    rows, frames = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert frames[0][0] == 0 and frames[-1][1] == whole.shape[0]
+    assert np.array_equal(rows, whole)
+
+
 @pytest.mark.parametrize("world", [2, 3])
 def test_ranks_merge_to_the_unsharded_result_over_gloo(tmp_path, world):
     import torch.multiprocessing as mp
@@ -204,3 +248,36 @@ def test_event_text_formats_match_the_reference_output(name):
         # the BolidMessage fields at full precision
         assert [np.float32(x) for x in d[:5]] == [f["noise"], f["peak_freq"], f["magnitude"], f["min_freq"], f["max_freq"]]
         assert int(d[6]) == f["end_sample"]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("chunk_frames,threads", [(64, 1), (100, 3)])
+def test_staged_reader_equals_the_one_shot_call(tmp_path, chunk_frames, threads):
+    """staged_compute (chunks through two pinned staging buffers, copy threads, in-place output) against
+    one ro_wf_process_host call on the whole shard: identical rows and records, chunk seams included."""
+    from radio_observer_b200 import synth
+    from radio_observer_b200.capi import DET_DTYPE
+    bins, overlap, sr = 16384, 12288, 96000
+    hop = bins - overlap
+    n = bins + 700 * hop + 11
+    iq = synth.generate_int16(synth.SynthSpec(sample_rate=sr, n_samples=n, seed=77, carrier_freq=26700.3,
+                                              meteor_band=(26450.0, 26550.0)))
+    path = str(tmp_path / "iq.npy")
+    np.save(path, iq)
+    iq_map = np.load(path, mmap_mode="r")
+    keys = dict(low_detect_freq=26450.0, hi_detect_freq=26550.0, low_noise_freq=26000.0, hi_noise_freq=26300.0,
+                avg_freq_range=40.0, advance_time=5.0, jitter_time=2.0)
+    b = A.bolid_bands(sr, bins, overlap, **keys)
+    band = (A.frequency_to_bin(26200.0, sr, bins), A.frequency_to_bin(26800.0, sr, bins))
+    one = A.default_compute(bins, overlap, sr, [band], b, 0)
+    s0, s1 = 5 * hop, n - 3
+    want_rows, want_det = one(np.ascontiguousarray(iq_map[2 * s0:2 * s1]))
+    staged = A.staged_compute(bins, overlap, sr, [band], b, 0, chunk_frames=chunk_frames, copy_threads=threads)
+    F = A.frame_count(s1 - s0, bins, overlap)
+    rows = np.zeros((F, band[1] - band[0]), dtype=np.float32)
+    det = np.zeros(F, dtype=DET_DTYPE)
+    assert staged(iq_map, s0, s1, rows, det) == F == len(want_rows)
+    assert np.array_equal(rows, want_rows)
+    for k in ("noise", "peak", "avg"):
+        assert np.array_equal(det[k], want_det[k])
+    staged.close()

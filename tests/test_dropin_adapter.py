@@ -25,7 +25,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
 
 from radio_observer_b200 import synth
-from helpers import FLOOR_PEAK, REL_TOL, assert_rows_close, load_golden
+from helpers import FLOOR_PEAK, REL_TOL, assert_rows_close, bands_from_cfg, load_golden, recorder_cfg
+from oracle import ref_numpy as R
 from make_golden import read_fits
 
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "ref_oracle")
@@ -50,7 +51,11 @@ def run_pipeline(binary, g, factory, tmp, extra=None, flags=(), tag=None, iq=Non
         synth.write_wav(wav, g["iq"] if iq is None else iq, g["sample_rate"])
     # the reference starts recorder threads from a base-class constructor and now and then
     # aborts with "pure virtual method called" before reading any sample: retry
-    for attempt in range(25):
+    for attempt in range(60):
+        if attempt:
+            RETRIES["crash"] += 1
+            RETRIES["crash_" + os.path.basename(binary)] = RETRIES.get("crash_" + os.path.basename(binary), 0) + 1
+            print("[dropin] %s exited with %d before the stream (reference start-up race), run again" % (os.path.basename(binary), r.returncode))
         for sub in ("OUT", "dump"):
             shutil.rmtree(os.path.join(d, sub))
             os.makedirs(os.path.join(d, sub))
@@ -82,161 +87,209 @@ def run_pipeline(binary, g, factory, tmp, extra=None, flags=(), tag=None, iq=Non
     return out
 
 
-def _retry_reference_races(fn, *args, attempts=4):
-    """Both binaries are the REFERENCE's Pipeline, and the reference formats file names and DATE-OBS
-    with the non-reentrant gmtime() from several threads at once (src/WFTime.cpp:25-30): now and then a
-    name or a date card of either run carries another thread's time.  That race is not on the path
-    under test; a comparison that trips over it is repeated from scratch."""
-    for i in range(attempts):
-        try:
-            return fn(*args)
-        except AssertionError:
-            if i == attempts - 1:
-                raise
+RETRIES = {"crash": 0, "name_race": 0}      # counted and printed, never silent
 
 
-@pytest.mark.gpu
-@pytest.mark.parametrize("name,batch", [("n2048", 1), ("c2b_16k", 1), ("c2b_16k", 7)])
-def test_cuda_backend_is_a_drop_in(name, batch):
-    _retry_reference_races(_dropin_once, name, batch)
+def _kind(fn):
+    return fn.rsplit("_", 1)[-1].split(".")[0]          # snap / blid / raws
 
 
-@pytest.mark.gpu
-@pytest.mark.parametrize("name,batch", [("n2048", 1), ("c2b_16k", 1), ("c2b_16k", 64)])
-def test_narrow_ingest_is_a_drop_in(name, batch):
-    """SURVEY 8f N2: NarrowWAVStream -> CudaWaterfallBackend::processRaw (int16 all the way to the GPU)
-    against the stock WAVStream -> WaterfallBackend, same checks as the Complex path."""
-    _retry_reference_races(_dropin_once, name, batch, True)
+def _card(cards, key):
+    for c in cards:
+        if c.startswith(key.ljust(8) + "="):
+            return c
+    return ""
 
 
-def _dropin_once(name, batch, narrow=False):
+def _paired_files(ref, got):
+    """Files of the two runs paired WITHOUT their names: per kind, ordered by (CRVAL2, NAXIS2)."""
+    def order(run):
+        out = {}
+        for fn, f in run["fits"].items():
+            out.setdefault(_kind(fn), []).append((_card(f["cards"], "CRVAL2"), f["shape"], fn))
+        return {k: [x[2] for x in sorted(v)] for k, v in out.items()}
+    ro, go = order(ref), order(got)
+    assert {k: len(v) for k, v in ro.items()} == {k: len(v) for k, v in go.items()}, (ro, go)
+    return [(a, b) for k in sorted(ro) for a, b in zip(ro[k], go[k])]
+
+
+RACY = ("DATE-OBS=",)     # formatted with the non-reentrant gmtime(), like the file names
+
+
+def compare_runs(ref, got, g, *, rawmark_exact, rows_available, gpu_detector):
+    """Everything but file names and DATE-OBS: never retried.  Returns the list of name / DATE-OBS
+    differences (the reference's gmtime race, src/WFTime.cpp:25-30) for the caller to judge."""
+    name = g["meta"].get("name", "")
+    d = bands_from_cfg(g) if recorder_cfg(g, "bolid") else None
+    # 1. framing, row numbering, handles: exact
+    assert len(got["info"]) == len(ref["info"])
+    for k in ("mark", "sec", "usec"):
+        assert np.array_equal(got["info"][k], ref["info"][k]), k
+    if rawmark_exact:       # raw-ring marks are taken at frame time; identical when rows are not delayed
+        assert np.array_equal(got["info"]["rawmark"], ref["info"]["rawmark"])
+    # 2. rows
+    peak = np.abs(ref["rows"]).max(axis=1)
+    if rows_available:
+        assert_rows_close(got["rows"], ref["rows"], "%s adapter rows" % name)
+    # 3. detector statistics: the stock BolidRecorder on the stock rows against either the stock code on
+    #    the GPU rows (full rows) or the GPU's records (bands)
+    ties = []
+    if d is not None:
+        assert len(got["npa"]) == len(ref["npa"])
+        sr, bins = g["meta"]["sample_rate"], g["meta"]["bins"]
+        fq = np.array([R.bin_to_frequency(d.low_detect_bin + p, sr, bins) for p in range(d.detect_width)], dtype=np.float32)
+        def to_bin(freqs):
+            idx = np.array([int(np.argmin(np.abs(fq - f))) for f in freqs])
+            assert np.array_equal(fq[idx], freqs.astype(np.float32)), "peak frequency is not a bin frequency"
+            return idx
+        rp, gp = to_bin(ref["npa"]["peakfreq"]), to_bin(got["npa"]["peakfreq"])
+        floor = FLOOR_PEAK * peak
+        tol_n = np.maximum(REL_TOL * np.abs(ref["npa"]["noise"]), 4 * floor)
+        assert (np.abs(got["npa"]["noise"].astype(np.float64) - ref["npa"]["noise"]) <= tol_n).all()
+        same = rp == gp
+        tol_a = np.maximum(REL_TOL * np.abs(ref["npa"]["mag"]), 2 * floor)
+        assert (np.abs(got["npa"]["mag"].astype(np.float64) - ref["npa"]["mag"])[same] <= tol_a[same]).all()
+        for r in np.nonzero(~same)[0]:
+            row = ref["rows"][r].astype(np.float64)
+            a, b = row[d.low_detect_bin + gp[r]], row[d.low_detect_bin + rp[r]]
+            tol = 2 * max(REL_TOL * abs(b), floor[r])
+            ties.append((int(r), int(rp[r]), int(gp[r]), abs(a - b) / tol))
+        print("[dropin] %s: %d rows, peak bin identical in %d, %d tie(s) accepted (row, stock bin, gpu bin, margin/tol): %s"
+              % (name, len(same), int(same.sum()), len(ties),
+                 ", ".join("(%d, %d, %d, %.2f)" % t for t in ties[:25]) + (" ..." if len(ties) > 25 else "")))
+        assert all(t[3] <= 1.0 for t in ties), [t for t in ties if t[3] > 1.0]
+        assert len(ties) <= 0.03 * len(same)
+    # 4. bolid events: same count; band identical, peak frequency within a bin, raw-sample span identical
+    eb = [l.split(";") for l in ref["bolid"].strip().splitlines()]
+    gb = [l.split(";") for l in got["bolid"].strip().splitlines()]
+    assert len(eb) == len(gb), (ref["bolid"], got["bolid"])
+    for e, q in zip(eb, gb):
+        assert e[3:5] == q[3:5]             # minFreq, maxFreq
+        assert e[5:] == q[5:]               # startSample, endSample
+        assert abs(float(e[1]) - float(q[1])) <= 2 * float(ref_df(g))
+    # 5. FITS files, paired without their names: shapes, header cards, pixels
+    racy = []
+    pairs = _paired_files(ref, got)
+    for fa, fb in pairs:
+        a, b = ref["fits"][fa], got["fits"][fb]
+        assert a["shape"] == b["shape"], (fa, fb)
+        ca = [c for c in a["cards"] if not c.startswith(RACY)]
+        cb = [c for c in b["cards"] if not c.startswith(RACY)]
+        assert ca == cb, (fa, [x for x in zip(ca, cb) if x[0] != x[1]])
+        if "raws" in fa:
+            if rawmark_exact:
+                assert np.array_equal(a["data"], b["data"]), fa       # raw I/Q: untouched by the GPU
+        else:
+            err = np.abs(a["data"].astype(np.float64) - b["data"])
+            assert (err <= np.maximum(REL_TOL * np.abs(a["data"]), FLOOR_PEAK * peak.max())).all(), fa
+        if fa != fb:
+            racy.append(("name", fa, fb))
+        da, db = _card(a["cards"], "DATE-OBS"), _card(b["cards"], "DATE-OBS")
+        if da != db:
+            racy.append(("DATE-OBS", da, db))
+    # CSV metadata: CsvLog starts a new file whenever an entry's hour differs from the open file's
+    # (src/CsvLog.cpp:12-58); snapshot entries carry stream time (1970) and come from the writer threads,
+    # bolid entries carry the wall clock and come from the producer, so how the lines spread over files
+    # depends on thread timing.  The lines themselves must be the same: one per file written, same names.
+    def csv_names(run):
+        out = []
+        for txt in run["csv"].values():
+            out += [l.split(";")[0] for l in txt.splitlines() if l and not l.startswith("#")]
+        return sorted(out)
+    if not racy:
+        assert csv_names(got) == csv_names(ref)
+    else:
+        assert len(csv_names(got)) == len(csv_names(ref))
+    return racy, len(pairs), len(eb)
+
+
+def run_both(g, tmp, cuda_extra, *, narrow=False, dump_rows=True, iq=None, **kw):
+    """Stock backend and CUDA backend on the same WAV, compared.  File names and DATE-OBS are formatted
+    with the non-reentrant gmtime() from several threads (reference src/WFTime.cpp:25-30, src/WFTime.h:131,150):
+    a difference confined to them lets BOTH runs be repeated ONCE, and the repeat is counted and printed."""
+    for attempt in range(2):
+        for sub in ("waterfall", "waterfall_cuda"):
+            shutil.rmtree(os.path.join(tmp, sub), ignore_errors=True)
+        ref = run_pipeline(REF_BIN, g, "waterfall", tmp, iq=iq)        # stock rows are always dumped: they set the tolerances
+        got = run_pipeline(CUDA_BIN, g, "waterfall_cuda", tmp, cuda_extra, flags=("-N",) if narrow else (),
+                           iq=iq, dump_rows=dump_rows)
+        racy, n_files, n_events = compare_runs(ref, got, g, rows_available=dump_rows, **kw)
+        if not racy:
+            return ref, got, n_files, n_events
+        RETRIES["name_race"] += 1
+        print("[dropin] gmtime race in file names / DATE-OBS (repeat %d of 1): %s" % (attempt + 1, racy[:4]))
+    raise AssertionError("file names / DATE-OBS differ in two consecutive runs: %r" % (racy[:6],))
+
+
+def _need_binaries():
     if not (os.path.exists(REF_BIN) and os.path.exists(CUDA_BIN)):
         pytest.fail("prebuilt binaries missing: run __graft_entry__.build() in the build container")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,batch,narrow", [("n2048", 1, False), ("c2b_16k", 1, False), ("c2b_16k", 64, False),
+                                                 ("n2048", 1, True), ("c2b_16k", 7, True)])
+def test_cuda_backend_is_a_drop_in(name, batch, narrow):
+    """The default mode: the host receives the recorders' band and the GPU's detector records; the
+    recorder subclasses run the state machine on them.  Rows, handles, events, files against the stock
+    backend; narrow = NarrowWAVStream -> processRaw."""
+    _need_binaries()
     g = load_golden(name)
+    g["meta"]["name"] = "%s batch %d%s" % (name, batch, " narrow" if narrow else "")
     tmp = tempfile.mkdtemp(prefix="ro_dropin_")
     try:
-        ref = run_pipeline(REF_BIN, g, "waterfall", tmp)
-        # File names are formatted with the non-reentrant gmtime() from the producer thread and
-        # from every recorder's writer thread at once (reference src/WFTime.cpp:25-30,
-        # src/WFTime.h:131,150).  With the DSP on the GPU the producer no longer spends its time
-        # in FFTs, the threads collide more often, and now and then a name carries another
-        # thread's date (seen: 19700101000000 + 394 ms instead of 19700101000004 + 394 ms).
-        # That race is the reference's; rerun when only the names differ.
-        for attempt in range(6):
-            got = run_pipeline(CUDA_BIN, g, "waterfall_cuda", tmp, {"cuda_batch_frames": batch},
-                               flags=("-N",) if narrow else ())
-            if sorted(got["fits"]) == sorted(ref["fits"]):
-                break
-            shutil.rmtree(os.path.join(tmp, "waterfall_cuda"))
-        # the stock run must reproduce the committed golden (same reference code)
-        assert len(ref["rows"]) == g["meta"]["rows"]
-        assert np.array_equal(ref["info"], g["rowinfo"])
-        # 1. framing, row numbering, handles: exact
-        assert len(got["rows"]) == len(ref["rows"])
-        assert np.array_equal(got["info"]["mark"], ref["info"]["mark"])
-        assert np.array_equal(got["info"]["sec"], ref["info"]["sec"])
-        assert np.array_equal(got["info"]["usec"], ref["info"]["usec"])
-        if batch == 1:      # raw-ring marks are taken at frame time; identical when rows are not delayed
-            assert np.array_equal(got["info"]["rawmark"], ref["info"]["rawmark"])
-        # 2. rows
-        assert_rows_close(got["rows"], ref["rows"], "%s adapter rows" % name)
-        # 3. detector statistics computed by the UNMODIFIED BolidRecorder on the GPU rows
-        assert len(got["npa"]) == len(ref["npa"])
-        peak = np.abs(ref["rows"]).max(axis=1)
-        same_peak = got["npa"]["peakfreq"] == ref["npa"]["peakfreq"]
-        tol = np.maximum(REL_TOL * np.abs(ref["npa"]["mag"]), 2 * FLOOR_PEAK * peak)
-        assert (np.abs(got["npa"]["mag"].astype(np.float64) - ref["npa"]["mag"])[same_peak] <= tol[same_peak]).all()
-        tol_n = np.maximum(REL_TOL * np.abs(ref["npa"]["noise"]), 4 * FLOOR_PEAK * peak)
-        assert (np.abs(got["npa"]["noise"].astype(np.float64) - ref["npa"]["noise"]) <= tol_n).all()
-        print("[dropin] %s: rows %d, identical peak bin in %d rows" % (name, len(ref["rows"]), int(same_peak.sum())))
-        assert same_peak.mean() > 0.97          # argmax ties between near-equal noise bins only
-        # 4. bolid events: same count; start/end samples and frequencies identical
-        eb = [l.split(";") for l in ref["bolid"].strip().splitlines()]
-        gb = [l.split(";") for l in got["bolid"].strip().splitlines()]
-        assert len(eb) == len(gb) and len(eb) >= 1
-        for e, q in zip(eb, gb):
-            assert e[3:5] == q[3:5]             # minFreq, maxFreq
-            if batch == 1:
-                assert e[5:] == q[5:]           # startSample, endSample (raw-ring positions)
-            assert abs(float(e[1]) - float(q[1])) <= 2 * float(ref_df(g))     # peak frequency within one bin
-        # 5. FITS files: same names, same header cards (CRVAL/CDELT/CRPIX/CTYPE/NAXIS...), pixels in tolerance
-        assert sorted(got["fits"]) == sorted(ref["fits"]), (sorted(got["fits"]), sorted(ref["fits"]), got["bolid"], ref["bolid"])
-        n_checked = 0
-        for fn in ref["fits"]:
-            a, b = ref["fits"][fn], got["fits"][fn]
-            assert a["shape"] == b["shape"], fn
-            assert a["cards"] == b["cards"], (fn, [x for x in zip(a["cards"], b["cards"]) if x[0] != x[1]])
-            if "raws" in fn:
-                assert np.array_equal(a["data"], b["data"]), fn       # raw I/Q: untouched by the GPU
-            else:
-                w = a["shape"][0]
-                ra, rb = a["data"].reshape(-1, w), b["data"].reshape(-1, w)
-                # floor from the full row's peak is not available here; the band's own peak is smaller -> stricter
-                err = np.abs(ra.astype(np.float64) - rb)
-                fl = FLOOR_PEAK * np.abs(ref["rows"]).max()
-                assert (err <= np.maximum(REL_TOL * np.abs(ra), fl)).all(), fn
-            n_checked += 1
-        assert n_checked >= 2
-        assert sorted(got["csv"]) == sorted(ref["csv"]) or len(got["csv"]) == len(ref["csv"])
+        ref, got, n_files, n_events = run_both(g, tmp, {"cuda_batch_frames": batch}, narrow=narrow, dump_rows=False,
+                                               rawmark_exact=True, gpu_detector=True)
+        assert len(ref["rows"]) == g["meta"]["rows"] and np.array_equal(ref["info"], g["rowinfo"])   # stock run == golden
+        timing = json.load(open(os.path.join(tmp, "waterfall_cuda", "dump", "timing.json")))
+        assert timing["full_rows"] is False and timing["band"][1] - timing["band"][0] < g["meta"]["bins"] // 8
+        assert n_files >= 3 and n_events >= 1
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("narrow", [False, True])
-def test_long_run_that_laps_the_row_ring(narrow):
-    _retry_reference_races(_lapping_once, narrow)
+@pytest.mark.parametrize("name,batch,narrow", [("n2048", 1, False), ("c2b_16k", 7, False), ("c2b_16k", 64, True)])
+def test_cuda_backend_full_rows_mode(name, batch, narrow):
+    """cuda_rows = "full": whole rows come back and the reference's own BolidRecorder::update() runs on
+    them (the comparison mode): every bin of every row is checked."""
+    _need_binaries()
+    g = load_golden(name)
+    g["meta"]["name"] = "%s full rows batch %d" % (name, batch)
+    tmp = tempfile.mkdtemp(prefix="ro_dropin_full_")
+    try:
+        ref, got, n_files, n_events = run_both(g, tmp, {"cuda_batch_frames": batch, "cuda_rows": "full"}, narrow=narrow,
+                                               dump_rows=True, rawmark_exact=True, gpu_detector=False)
+        assert got["rows"].shape == ref["rows"].shape and n_files >= 3 and n_events >= 1
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
 
 
-def _lapping_once(narrow):
-    """The recorders' worker threads read the row ring, the handle table and the raw ring after the
+@pytest.mark.gpu
+@pytest.mark.parametrize("narrow,slow_ms", [(False, 0), (True, 0), (True, 150)])
+def test_long_run_that_laps_the_row_ring(narrow, slow_ms):
+    """The recorders' worker threads read the row ring, the handle table and the raw samples after the
     fact (reference src/WaterfallBackend.cpp:60-108); nothing in the reference stops the producer from
     overwriting what a queued snapshot still needs.  300 s of station I/Q lap the golden configuration's
     ring (752 rows = 32 s) nine times, and behind the CUDA backend the producer outruns the FITS
     writers: without the adapter's back-pressure (CudaWaterfallBackend::waitForWriters) files come out
-    with rows, times and names of one ring capacity later.  Same files as the stock backend expected."""
-    if not (os.path.exists(REF_BIN) and os.path.exists(CUDA_BIN)):
-        pytest.fail("prebuilt binaries missing: run __graft_entry__.build() in the build container")
+    with rows, times and names of one ring capacity later.  slow_ms delays every FITS write (config key
+    cuda_debug_write_delay_ms), so that a writer lags by a whole ring and the producer has to stop at
+    the exact row whose push would overwrite the queued snapshot's handle slot."""
+    _need_binaries()
     g = load_golden("c2b_16k")
+    g["meta"]["name"] = "lap%s%s" % (" narrow" if narrow else "", " slow writer" if slow_ms else "")
     sr = g["sample_rate"]
     spec = synth.SynthSpec(sample_rate=sr, n_samples=300 * sr, seed=0x1A9, carrier_freq=26700.3,
                            meteor_band=(26450.0, 26550.0))
     iq = synth.generate_int16(spec)
     tmp = tempfile.mkdtemp(prefix="ro_dropin_lap_")
     try:
-        # no -r row dump for 7000 rows of 64 KB: rows are compared through the FITS files
-        ref = run_pipeline(REF_BIN, g, "waterfall", tmp, iq=iq, dump_rows=False)
-        for attempt in range(6):            # the reference's gmtime race, see _dropin_once
-            got = run_pipeline(CUDA_BIN, g, "waterfall_cuda", tmp, {"cuda_batch_frames": 64},
-                               flags=("-N",) if narrow else (), iq=iq, dump_rows=False)
-            if sorted(got["fits"]) == sorted(ref["fits"]):
-                break
-            shutil.rmtree(os.path.join(tmp, "waterfall_cuda"))
-        assert len(ref["info"]) > 8 * 752
-        for k in ("mark", "sec", "usec"):
-            assert np.array_equal(got["info"][k], ref["info"][k])
-        eb = [l.split(";") for l in ref["bolid"].strip().splitlines()]
-        gb = [l.split(";") for l in got["bolid"].strip().splitlines()]
-        assert len(eb) == len(gb) and len(eb) >= 10
-        for e, q in zip(eb, gb):
-            assert e[3:5] == q[3:5]
-        only_ref = sorted(set(ref["fits"]) - set(got["fits"]))
-        only_got = sorted(set(got["fits"]) - set(ref["fits"]))
-        assert not only_ref and not only_got, (len(ref["fits"]), only_ref[:5], only_got[:5])
-        peak = max(float(np.abs(v["data"]).max()) for fn, v in ref["fits"].items() if "raws" not in fn)
-        for fn in ref["fits"]:
-            a, b = ref["fits"][fn], got["fits"][fn]
-            assert a["shape"] == b["shape"], fn
-            assert a["cards"] == b["cards"], (fn, [x for x in zip(a["cards"], b["cards"]) if x[0] != x[1]])
-            if "raws" in fn:
-                assert np.array_equal(a["data"], b["data"]), fn
-            else:
-                # the full row's peak is not in the file: the largest pixel of any file of this run (the carrier
-                # is inside the recorded band) stands in for it
-                err = np.abs(a["data"].astype(np.float64) - b["data"])
-                assert (err <= np.maximum(REL_TOL * np.abs(a["data"]), FLOOR_PEAK * peak)).all(), fn
-        print("[dropin lap] %d rows, %d events, %d FITS files identical in name, header and raw I/Q"
-              % (len(ref["info"]), len(eb), len(ref["fits"])))
+        ref, got, n_files, n_events = run_both(g, tmp, {"cuda_batch_frames": 64, "cuda_debug_write_delay_ms": slow_ms},
+                                               narrow=narrow, dump_rows=False, iq=iq, rawmark_exact=True, gpu_detector=True)
+        assert len(ref["info"]) > 8 * 752 and n_events >= 10
+        print("[dropin lap] %d rows, %d events, %d FITS files identical in header, pixels (tolerance) and raw I/Q"
+              % (len(ref["info"]), n_events, n_files))
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
 
@@ -244,46 +297,56 @@ def _lapping_once(narrow):
 @pytest.mark.gpu
 @pytest.mark.parametrize("name", ["n2048", "c2b_16k"])
 def test_cuda_backend_fp64_reproduces_the_stock_backend(name):
-    _retry_reference_races(_dropin_fp64_once, name)
-
-
-def _dropin_fp64_once(name):
     """cuda_precision = 1: the reference's Pipeline with the CUDA backend in double precision gives the
     stock backend's rows to the last float ulp, hence the same detector statistics, events and files."""
-    if not (os.path.exists(REF_BIN) and os.path.exists(CUDA_BIN)):
-        pytest.fail("prebuilt binaries missing: run __graft_entry__.build() in the build container")
+    _need_binaries()
     g = load_golden(name)
+    g["meta"]["name"] = name + " fp64"
     tmp = tempfile.mkdtemp(prefix="ro_dropin64_")
     try:
-        ref = run_pipeline(REF_BIN, g, "waterfall", tmp)
-        for attempt in range(6):            # the reference's gmtime race, see above
-            got = run_pipeline(CUDA_BIN, g, "waterfall_cuda", tmp, {"cuda_batch_frames": 1, "cuda_precision": 1})
-            if sorted(got["fits"]) == sorted(ref["fits"]):
-                break
-            shutil.rmtree(os.path.join(tmp, "waterfall_cuda"))
-        assert got["rows"].shape == ref["rows"].shape
+        ref, got, n_files, n_events = run_both(g, tmp, {"cuda_batch_frames": 1, "cuda_precision": 1, "cuda_rows": "full"},
+                                               dump_rows=True, rawmark_exact=True, gpu_detector=False)
         ulp = np.spacing(np.abs(ref["rows"]))
         assert (np.abs(got["rows"] - ref["rows"]) <= ulp).all()
         same = float((got["rows"] == ref["rows"]).mean())
         print("[dropin fp64] %s: %.4f %% of pixels bit-identical, the rest one ulp apart" % (name, 100 * same))
         assert same > 0.99
-        for k in ("mark", "sec", "usec", "rawmark"):
-            assert np.array_equal(got["info"][k], ref["info"][k])
         # detector statistics of the unmodified BolidRecorder: identical unless a one-ulp pixel is involved
         assert np.array_equal(got["npa"]["peakfreq"], ref["npa"]["peakfreq"])
         assert np.allclose(got["npa"]["noise"], ref["npa"]["noise"], rtol=2e-7, atol=0)
         assert np.allclose(got["npa"]["mag"], ref["npa"]["mag"], rtol=2e-7, atol=0)
-        assert got["bolid"].strip().splitlines().__len__() == ref["bolid"].strip().splitlines().__len__() >= 1
         for e, q in zip(ref["bolid"].strip().splitlines(), got["bolid"].strip().splitlines()):
-            e, q = e.split(";"), q.split(";")
-            assert e[1] == q[1] and e[3:] == q[3:]          # peak frequency, band, start/end samples
-        assert sorted(got["fits"]) == sorted(ref["fits"])
-        for fn in ref["fits"]:
-            a, b = ref["fits"][fn], got["fits"][fn]
-            assert a["shape"] == b["shape"] and a["cards"] == b["cards"], fn
-            assert (np.abs(a["data"].astype(np.float64) - b["data"]) <= np.spacing(np.abs(a["data"]))).all(), fn
+            assert e.split(";")[1] == q.split(";")[1]           # peak frequency
+        for fa, fb in _paired_files(ref, got):
+            a, b = ref["fits"][fa], got["fits"][fb]
+            assert (np.abs(a["data"].astype(np.float64) - b["data"]) <= np.spacing(np.abs(a["data"]))).all(), fa
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
+
+
+@pytest.mark.gpu
+def test_no_silent_retries():
+    """Runs last in this file: what the drop-in tests above had to repeat."""
+    print("[dropin] retries in this session: %r" % (RETRIES,))
+    # crash = a binary died before reading a sample: the reference creates its recorder threads in a
+    # base-class constructor (cppapp/cppapp/Thread.cpp:47-56), and when the new thread runs first the
+    # process ends in "pure virtual method called" or a segmentation fault.  It comes in bursts (ten in a
+    # row have been seen with the stock backend); the CUDA backend's recorders start their threads
+    # differently (CudaRecorders.h) and are not expected in this count.
+    assert RETRIES["name_race"] <= 2, RETRIES
+
+
+def _retry_reference_races(fn, *args, attempts=2):
+    """CPU-only comparisons of two REFERENCE pipelines (stock backend behind two frontends): the same
+    gmtime race can hit either side; one counted repeat."""
+    for i in range(attempts):
+        try:
+            return fn(*args)
+        except AssertionError:
+            if i == attempts - 1:
+                raise
+            RETRIES["name_race"] += 1
+            print("[dropin] comparison repeated once (reference gmtime race)")
 
 
 @pytest.mark.parametrize("tail", [0, 1, 300, 512])

@@ -75,15 +75,16 @@ def test_rows_match_oracle_large(bins, overlap):
     wf.close()
 
 
-def test_long_frames_cross_scratch_batches(monkeypatch):
-    """N > 16384 runs as split kernel + per-class transforms over a cache-sized scratch; with a
-    1 MiB budget the scratch holds one wave (74 frames of 32k), so 200 frames take three batches."""
-    monkeypatch.setenv("RO_SCRATCH_MB", "1")
+def test_long_frames_cross_scratch_batches():
+    """The split path (radix-Na step through a scratch, then Na transforms per frame) with a 1 MiB
+    scratch budget: the scratch holds one wave (74 frames of 32k), so 200 frames take three batches.
+    32k frames take the fused kernel by default; cfg.tuning sends them through the split path here."""
     bins, overlap = 32768, 24576
     n = bins + 199 * (bins - overlap) + 17
     iq = station_iq(n, 96000, seed=99)
-    wf = ro.Waterfall(bins, overlap, sample_rate=96000, in_format=ro.IN_INT16)
+    wf = ro.Waterfall(bins, overlap, sample_rate=96000, in_format=ro.IN_INT16, tuning=ro.TUNE_NO_FUSED, scratch_mb=1)
     rows, _, nf = wf.process_host(iq)
+    assert "wf_split_kernel" in wf.kernel_name()
     ref = R.waterfall_rows(iq, bins, overlap)
     assert nf == len(ref) == 200
     assert_rows_close(rows, ref, "N=32768, 200 frames, 3 scratch batches")
@@ -104,11 +105,11 @@ def test_rows_match_oracle_float32_and_gain(bins, overlap):
 
 
 @pytest.mark.parametrize("overlap,iq_gain", [(24576, 0.125), (16384, 0.0), (3, 0.0)])
-def test_float32_32k_fused_many_frames_per_cta(overlap, iq_gain, monkeypatch):
+def test_float32_32k_fused_many_frames_per_cta(overlap, iq_gain):
     """float32 frames of 32768 points run in ONE kernel (MODE_FUSED1_F32: radix-2 step + two 16k
     transforms per frame).  400 frames make every CTA of the persistent grid walk several frames
     (its private scratch slice is rewritten per frame); the same input through the split path
-    (RO_NO_FUSED_F32=1) is the second witness."""
+    (cfg.tuning = RO_TUNE_NO_FUSED) is the second witness."""
     bins = 32768
     n_frames = 400 if overlap else 60
     n = bins + (n_frames - 1) * (bins - overlap) + 5
@@ -120,8 +121,7 @@ def test_float32_32k_fused_many_frames_per_cta(overlap, iq_gain, monkeypatch):
     ref = R.waterfall_rows(iq, bins, overlap, iq_gain=iq_gain)
     assert nf == len(ref) == n_frames
     assert_rows_close(rows, ref, f"float32 fused N=32768 ov={overlap}")
-    monkeypatch.setenv("RO_NO_FUSED_F32", "1")
-    wf2 = ro.Waterfall(bins, overlap, sample_rate=96000, in_format=ro.IN_FLOAT32, iq_gain=iq_gain)
+    wf2 = ro.Waterfall(bins, overlap, sample_rate=96000, in_format=ro.IN_FLOAT32, iq_gain=iq_gain, tuning=ro.TUNE_NO_FUSED)
     rows2, _, nf2 = wf2.process_host(iq)
     wf2.close()
     assert nf2 == nf

@@ -84,6 +84,24 @@ def test_planned_files_match_what_the_reference_wrote(name, tmp_path):
         assert hashlib.sha256(np.ascontiguousarray(data).tobytes()).hexdigest() == want["sha256"]
         n_px += 1
     assert n_px >= 1
+    # --- 8f N3: the raw-I/Q file that goes with every bolid file, cut from the archive's own samples
+    rows_buf = 8 * max(P.snapshot_rows(snap["snapshot_length"], A.fft_sample_rate(sr, bins, ov)),
+                       P.snapshot_rows(bol["snapshot_length"], A.fft_sample_rate(sr, bins, ov)))
+    cap = P.raw_ring_capacity(rows_buf, sample_rate=sr, bins=bins, overlap=ov)
+    n_raw = 0
+    for p in bplan:
+        name = P.raw_file_name(p, "gold")
+        want = g["fits"][name]
+        first, count = P.raw_extent(p, sample_rate=sr, bins=bins, overlap=ov, ring_capacity=cap)
+        assert want["shape"] == [2, count], name
+        path = str(tmp_path / name)
+        P.write_raw(path, p, g["iq"], sample_rate=sr, bins=bins, overlap=ov, ring_capacity=cap, origin="gold")
+        cards, hdr, data = F.read_image(path)
+        assert [c for c in cards if not c.startswith(SKIP)] == [c for c in want["cards"] if not c.startswith(SKIP)], name
+        if first + count <= len(g["iq"]) // 2:         # beyond the end of the stream the reference wrote what its ring held
+            assert hashlib.sha256(np.ascontiguousarray(data).tobytes()).hexdigest() == want["sha256"], name
+            n_raw += 1
+    assert n_raw >= 1
 
 
 def test_event_cut_short_by_the_end_of_the_stream_gets_no_file(tmp_path):

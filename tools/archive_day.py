@@ -25,6 +25,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from radio_observer_b200 import archive as A, synth      # noqa: E402
+from radio_observer_b200.capi import DET_DTYPE as A_DET  # noqa: E402
 
 SR, BINS, OVERLAP = 96000, 16384, 12288
 KEYS = dict(low_detect_freq=26450.0, hi_detect_freq=26550.0, low_noise_freq=26000.0, hi_noise_freq=26300.0,
@@ -37,6 +38,8 @@ def main():
     ap.add_argument("--dir", default="/dev/shm" if os.path.isdir("/dev/shm") else "/tmp")
     ap.add_argument("--out", default=None, help="write the snapshot / bolid FITS files and the metadata CSV here")
     ap.add_argument("--max-files", type=int, default=200, help="bound on FITS files written per recorder")
+    ap.add_argument("--chunk-frames", type=int, default=16384, help="frames per pinned staging buffer")
+    ap.add_argument("--copy-threads", type=int, default=4, help="threads copying the archive into the staging buffer")
     a = ap.parse_args()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -65,13 +68,16 @@ def main():
     iq = np.load(path, mmap_mode="r")
     b = A.bolid_bands(SR, BINS, OVERLAP, **KEYS)
     band = (A.frequency_to_bin(26200.0, SR, BINS), A.frequency_to_bin(26800.0, SR, BINS))
-    compute = A.default_compute(BINS, OVERLAP, SR, [band], b, local)
-    compute(np.ascontiguousarray(iq[:2 * (BINS * 8)]))           # warm-up: context, buffers
+    compute = A.default_compute(BINS, OVERLAP, SR, [band], b, local)      # seams, below
+    staged = A.staged_compute(BINS, OVERLAP, SR, [band], b, local, chunk_frames=a.chunk_frames, copy_threads=a.copy_threads)
+    warm_r = np.empty((8, band[1] - band[0]), dtype=np.float32)
+    warm_d = np.zeros(8, dtype=A_DET)
+    staged(iq, 0, BINS + 7 * (BINS - OVERLAP), warm_r, warm_d)      # warm-up: context, buffers
     if dist is not None:
         dist.barrier()
     t0 = time.time()
     rows, det, shards = A.reprocess_archive(iq, BINS, OVERLAP, sample_rate=SR, bands=[band], detector=b,
-                                            rank=rank, world=world, dist=dist, compute=compute)
+                                            rank=rank, world=world, dist=dist, shared_dir=a.dir, staged=staged)
     t_all = time.time() - t0
     if rank == 0:
         F = A.frame_count(n_total, BINS, OVERLAP)
@@ -98,17 +104,24 @@ def main():
             times = P.frame_times(int(F), BINS, OVERLAP, SR, block=1024)
             common = dict(sample_rate=SR, bins=BINS, overlap=OVERLAP, origin="archive")
             snaps = P.plan_snapshots(int(F), times, snapshot_length=60, **common)
-            blids = [p for p in P.plan_bolids(trig.events, times, snapshot_length=60, n_rows=int(F), **common) if p.start_row >= 0]
+            blids = P.plan_bolids(trig.events, times, snapshot_length=60, n_rows=int(F), **common)
             with open(os.path.join(a.out, "archive_meta.csv"), "w") as csv:
                 csv.write("# file name; noise; peak f.; mag.; duration\n")
-                for p in blids:
+                for p in blids:         # every reported event has its line, also one that starts before row 0
                     f = A.event_fields(p.event, sample_rate=SR, bins=BINS, overlap=OVERLAP,
                                        low_detect_freq=KEYS["low_detect_freq"], hi_detect_freq=KEYS["hi_detect_freq"])
                     csv.write(A.bolid_csv_line(p.file_name, f) + "\n")
-            for p in snaps[:a.max_files] + blids[:a.max_files]:
+            cap = P.raw_ring_capacity(8 * P.snapshot_rows(60, A.fft_sample_rate(SR, BINS, OVERLAP)), sample_rate=SR, bins=BINS, overlap=OVERLAP)
+            n_raw = 0
+            for p in snaps[:a.max_files]:
                 P.write_planned(os.path.join(a.out, p.file_name), p, rows, left_bin=band[0], low_freq=26200.0, **common)
+            for p in blids[:a.max_files]:
+                if p.start_row >= 0:    # rows before the archive do not exist (the reference writes ring garbage there)
+                    P.write_planned(os.path.join(a.out, p.file_name), p, rows, left_bin=band[0], low_freq=26200.0, **common)
+                P.write_raw(os.path.join(a.out, P.raw_file_name(p, "archive")), p, iq, ring_capacity=cap, **common)
+                n_raw += 1
             written = {"snapshots_planned": len(snaps), "bolids_planned": len(blids),
-                       "fits_written": min(len(snaps), a.max_files) + min(len(blids), a.max_files),
+                       "fits_written": min(len(snaps), a.max_files) + min(len(blids), a.max_files), "raw_iq_files": n_raw,
                        "seconds": round(time.time() - t2, 2)}
         line = {"tool": "archive_day", "hours": a.hours, "n_gpus": world, "samples": n_total, "frames": int(F),
                 "bins": BINS, "overlap": OVERLAP, "seconds_compute_and_merge": round(t_all, 3),
@@ -117,8 +130,10 @@ def main():
                 "events": len(trig.events), "seconds_trigger_fsm": round(t_trig, 3),
                 "seams_bit_identical": bool(seams_ok), "shards": [[s.frame0, s.frame1] for s in shards],
                 "seconds_generate_archive": round(t_gen, 1), "outputs": written,
-                "note": "host int16 archive in shared memory -> per-rank ro_wf_process_host -> rows of the recorder band + "
-                        "detector records gathered on rank 0 (gloo); no data-path collective"}
+                "chunk_frames": a.chunk_frames, "copy_threads": a.copy_threads,
+                "note": "host int16 archive in shared memory -> per rank: copy threads -> two pinned staging buffers -> "
+                        "ro_wf_process_host -> rows of the recorder band + detector records written in place into arrays "
+                        "all ranks map (no gather); gloo for two barriers; no data-path collective"}
         os.write(out_fd, (json.dumps(line) + "\n").encode())
     if dist is not None:
         dist.barrier()

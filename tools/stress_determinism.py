@@ -1,8 +1,7 @@
 #!/usr/bin/env python3
 """tools/stress_determinism.py -- race hunt: the same input through the device-resident path many
-times; every repetition must give bit-identical rows (prints one sha1 set per shape).  Run it under
-different RO_STAGGER / RO_SPLIT_* settings and diff the output: the arithmetic does not depend on
-them, so the digests must agree too.  Needs a GPU."""
+times; every repetition must give bit-identical rows (prints one sha1 set per shape).  32k frames run
+twice, through the fused kernel and (cfg.tuning = RO_TUNE_NO_FUSED) through the split path.  Needs a GPU."""
 import hashlib
 import sys
 import os
@@ -23,8 +22,9 @@ def main():
     d_iq = DeviceBuffer(iq.nbytes)
     d_iq.upload(iq)
     ok = True
-    for N, ov in [(4096, 3072), (8192, 6144), (16384, 12288), (16384, 0), (16384, 8192), (32768, 24576), (65536, 49152)]:
-        wf = ro.Waterfall(N, ov, sample_rate=96000)
+    for N, ov, tuning in [(4096, 3072, 0), (8192, 6144, 0), (16384, 12288, 0), (16384, 0, 0), (16384, 8192, 0),
+                          (32768, 24576, 0), (32768, 24576, ro.TUNE_NO_FUSED), (65536, 49152, 0)]:
+        wf = ro.Waterfall(N, ov, sample_rate=96000, tuning=tuning)
         F = wf.frame_count(S)
         d_rows = DeviceBuffer(4 * F * N)
         digests = set()
