@@ -469,7 +469,14 @@ def main():
             return 0
         return reference_arm(args, emit)
 
+    t_start = time.time()
+
+    def note(msg):
+        if rank == 0:
+            print("[bench %6.1f s] %s" % (time.time() - t_start, msg), file=sys.stderr, flush=True)
+
     placement = bind_to_gpu_cpus(local_rank, world)
+    note("placement %r" % (placement,))
 
     import torch
     import radio_observer_b200 as ro
@@ -505,6 +512,8 @@ def main():
                       device=local_rank)
     F = wf.frame_count(S)
     d_iq = [gen_iq_device(torch, S, 0x5EED0002 + 1000 * rank + g, dev) for g in range(G)]
+    torch.cuda.synchronize()
+    note("%d shard(s) of 2^%d samples generated on the device" % (G, args.log2_samples))
     d_rows = torch.empty(F * BINS, dtype=torch.float32, device=dev)
     d_det = torch.empty(F * 4, dtype=torch.int32, device=dev)
     # a dedicated non-default stream: the default stream's handle is 0, which the C ABI
@@ -542,6 +551,7 @@ def main():
     clocks = sampler.stop(t_wall0, t_wall1) if rank == 0 else None
     ms_per_step = ms_total / args.steps
     value = world * S * P / (ms_per_step * 1e-3) / 1e6
+    note("timed region done: %.3f ms per step" % ms_per_step)
 
     # ---- kernel times: a separate pass with the library's per-launch CUDA events on the same stream ----
     wf.set_profiling(True)
@@ -611,6 +621,7 @@ def main():
         del d_tmp
     except Exception:                               # noqa: BLE001
         h2d_gbs = None
+    note("concurrent H2D: %s GB/s per GPU" % h2d_gbs)
     e2e_steps = max(3, min(args.steps, 10))
     for _ in range(2):
         wf.process_host(h_iq.array, h_rows.array, h_det.array)
@@ -631,6 +642,7 @@ def main():
            "h2d_ceiling_msamples_per_s": (world * h2d_gbs * 1e9 / 4 / 1e6) if h2d_gbs else None,
            "placement": placement}
 
+    note("e2e done: %.1f Msamples/s" % e2e_value)
     cpu_baseline = cpu_alt = dropin = parity = fp64 = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         # ---- parity of the timed input: its first frames against the oracle (the checker), the tests' rule
@@ -682,6 +694,7 @@ def main():
         except Exception as e:                      # noqa: BLE001
             parity = {"error": "%s: %s" % (type(e).__name__, e)}
 
+        note("parity / fp64 done: %r" % (parity,))
         # ---- CPU baselines: 30 min of station data, about 12 s of work for the reference on one core ----
         secs = 1800.0
         from radio_observer_b200 import synth
@@ -704,6 +717,7 @@ def main():
                 cpu_baseline = {"value": v, "unit": "Msamples/s", "cores": 1, "kind": "port",
                                 "sample": "20 s of station I/Q through oracle/ref_numpy.py (numpy pocketfft)"}
             # the same path on scipy.fft, the as-shipped -O0 build, and what FFT library the box has
+            note("cpu_baseline done: %r" % (cpu_baseline["value"],))
             cpu_alt = {"fft_probe": fft_probe()}
             try:
                 iq120 = host_station_iq(120 * SR, 0x5EED0002)
@@ -723,6 +737,7 @@ def main():
             # the same WAV through the reference's own Pipeline with one string changed in the config
             # ("factory": "waterfall_cuda"): what a station operator gets.  Process start-up and CUDA
             # initialisation (about 1.3 s) are inside every figure; each variant runs twice.
+            note("cpu_baseline_alt done: %r" % (cpu_alt,))
             wf.close()
             if wav and os.path.exists(CUDA_BIN):
                 def variant(**kw):

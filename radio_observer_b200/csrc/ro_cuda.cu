@@ -132,6 +132,7 @@ struct ro_wf {
 	float *h_srows[2];                    // pinned host rows per slot (row_width)
 	ro_det_rec *h_sdet[2];
 	cudaEvent_t ev_slot[2];
+	bool   slot_used[2];
 	size_t slot_rows_cap;
 	int    cur;                           // slot being filled
 	size_t staged;                        // new samples in h_stage[cur]
@@ -989,17 +990,25 @@ int ensure_stream_buffers(ro_wf *h)
 	return RO_OK;
 }
 
-// wait for a batch and move its results out of the pinned slot
-int retire(ro_wf *h, Pending *p)
+// wait for a batch; with `move_out` its results leave the pinned slot (the slot is about to be reused)
+int retire(ro_wf *h, Pending *p, bool move_out)
 {
 	if (p->slot < 0) return RO_OK;
 	CU(cudaEventSynchronize(h->ev_slot[p->slot]));
+	if (!move_out) return RO_OK;
 	p->rows.assign(h->h_srows[p->slot], h->h_srows[p->slot] + p->n_rows * (size_t)h->row_width);
 	if (h->det_on) p->det.assign(h->h_sdet[p->slot], h->h_sdet[p->slot] + p->n_rows);
 	p->slot = -1;
 	return RO_OK;
 }
 
+// One batch of the streaming path, three streams (north_star: "pinned double-buffered staging with async
+// H2D copies on a side stream"):
+//   h2d_stream   new samples of the slot, once the kernels that last read this slot's device input are done
+//   own_stream   transform, (reduce,) detector, then the device-to-device carry of the overlap into the
+//                other slot
+//   d2h_stream   band rows and detector records into the slot's pinned buffers; ev_slot marks them ready
+// so the upload of batch k+1 and the download of batch k-1 run beside the kernels of batch k.
 int submit(ro_wf *h)
 {
 	const size_t total = h->carry + h->staged;
@@ -1007,30 +1016,42 @@ int submit(ro_wf *h)
 	const size_t F = G * (size_t)h->R;
 	if (F == 0) return RO_OK;
 	const int s = h->cur;
-	cudaStream_t st = h->own_stream;
+	cudaStream_t sc = h->own_stream;
 	unsigned char *d_in = (unsigned char *)h->d_sin[s];
-	if (h->staged)
+	if (h->staged) {
+		if (h->slot_used[s]) CU(cudaStreamWaitEvent(h->h2d_stream, h->ev_comp[s], 0));
 		CU(cudaMemcpyAsync(d_in + h->carry * (size_t)h->in_bytes, h->h_stage[s],
-		                   h->staged * (size_t)h->in_bytes, cudaMemcpyHostToDevice, st));
-	int rc = launch_fft(h, st, d_in, h->d_srows[s], h->N, (long long)F);
+		                   h->staged * (size_t)h->in_bytes, cudaMemcpyHostToDevice, h->h2d_stream));
+		CU(cudaEventRecord(h->ev_h2d[s], h->h2d_stream));
+		CU(cudaStreamWaitEvent(sc, h->ev_h2d[s], 0));
+	}
+	// the slot's device rows and records are free once their previous download is done
+	if (h->slot_used[s]) CU(cudaStreamWaitEvent(sc, h->ev_slot[s], 0));
+	int rc = launch_fft(h, sc, d_in, h->d_srows[s], h->N, (long long)F);
 	if (rc) return rc;
 	const float *d_out = h->d_srows[s];
 	if (h->red_on) {
-		rc = launch_reduce(h, st, h->d_srows[s], (long long)G, h->d_sred[s]);
+		rc = launch_reduce(h, sc, h->d_srows[s], (long long)G, h->d_sred[s]);
 		if (rc) return rc;
 		d_out = h->d_sred[s];
 	}
-	rc = launch_detect(h, st, d_out, h->out_bins, (long long)G, h->d_sdet[s]);
+	rc = launch_detect(h, sc, d_out, h->out_bins, (long long)G, h->d_sdet[s]);
 	if (rc) return rc;
-	rc = copy_rows_out(h, st, h->h_srows[s], d_out, G);
+	const size_t left = total - F * (size_t)h->hop;       // overlap carried to the next frame
+	if (left) {
+		// the other slot's input was last read by the kernels of the previous batch: same stream, in order;
+		// its upload region starts behind the carry, so the two copies do not meet
+		CU(cudaMemcpyAsync(h->d_sin[s ^ 1], d_in + F * (size_t)h->hop * (size_t)h->in_bytes,
+		                   left * (size_t)h->in_bytes, cudaMemcpyDeviceToDevice, sc));
+	}
+	CU(cudaEventRecord(h->ev_comp[s], sc));
+	CU(cudaStreamWaitEvent(h->d2h_stream, h->ev_comp[s], 0));
+	rc = copy_rows_out(h, h->d2h_stream, h->h_srows[s], d_out, G);
 	if (rc) return rc;
 	if (h->det_on)
-		CU(cudaMemcpyAsync(h->h_sdet[s], h->d_sdet[s], sizeof(ro_det_rec) * G, cudaMemcpyDeviceToHost, st));
-	const size_t left = total - F * (size_t)h->hop;       // overlap carried to the next frame
-	if (left)
-		CU(cudaMemcpyAsync(h->d_sin[s ^ 1], d_in + F * (size_t)h->hop * (size_t)h->in_bytes,
-		                   left * (size_t)h->in_bytes, cudaMemcpyDeviceToDevice, st));
-	CU(cudaEventRecord(h->ev_slot[s], st));
+		CU(cudaMemcpyAsync(h->h_sdet[s], h->d_sdet[s], sizeof(ro_det_rec) * G, cudaMemcpyDeviceToHost, h->d2h_stream));
+	CU(cudaEventRecord(h->ev_slot[s], h->d2h_stream));
+	h->slot_used[s] = true;
 
 	Pending *p = new (std::nothrow) Pending();
 	if (!p) return fail(RO_E_NOMEM, "out of memory");
@@ -1044,9 +1065,10 @@ int submit(ro_wf *h)
 	h->carry = left;
 	h->staged = 0;
 	h->cur = s ^ 1;
-	// the slot we are about to fill must be idle and its results saved
+	// the slot we are about to fill must be idle -- its upload done (ev_slot lies behind it) -- and results
+	// still waiting in its pinned buffers are moved out
 	for (Pending *q : h->pending)
-		if (q->slot == h->cur) { rc = retire(h, q); if (rc) return rc; }
+		if (q->slot == h->cur) { rc = retire(h, q, true); if (rc) return rc; }
 	return RO_OK;
 }
 
@@ -1101,14 +1123,17 @@ extern "C" int ro_wf_poll(ro_wf *h, float *rows, size_t max_rows, ro_det_rec *de
 	size_t got = 0;
 	while (got < max_rows && !h->pending.empty()) {
 		Pending *p = h->pending.front();
-		int rc = retire(h, p);
+		int rc = retire(h, p, false);
 		if (rc) { h->sticky_error = true; return rc; }
 		if (got == 0 && first_row) *first_row = p->first_row + p->consumed;
 		const size_t take = std::min(max_rows - got, p->n_rows - p->consumed);
+		// straight from the pinned slot unless the slot had to be vacated for a later batch
+		const float *src_rows = p->slot >= 0 ? h->h_srows[p->slot] : p->rows.data();
+		const ro_det_rec *src_det = p->slot >= 0 ? h->h_sdet[p->slot] : p->det.data();
 		if (rows)
-			memcpy(rows + got * (size_t)h->row_width, p->rows.data() + p->consumed * (size_t)h->row_width,
+			memcpy(rows + got * (size_t)h->row_width, src_rows + p->consumed * (size_t)h->row_width,
 			       take * (size_t)h->row_width * sizeof(float));
-		if (det && h->det_on) memcpy(det + got, p->det.data() + p->consumed, take * sizeof(ro_det_rec));
+		if (det && h->det_on) memcpy(det + got, src_det + p->consumed, take * sizeof(ro_det_rec));
 		p->consumed += take;
 		got += take;
 		if (p->consumed == p->n_rows) { h->pending.pop_front(); delete p; }
@@ -1121,7 +1146,10 @@ extern "C" int ro_wf_reset(ro_wf *h)
 {
 	if (!h) return fail(RO_E_INVALID, "null handle");
 	CU(cudaSetDevice(h->cfg.device));
+	CU(cudaStreamSynchronize(h->h2d_stream));
 	CU(cudaStreamSynchronize(h->own_stream));
+	CU(cudaStreamSynchronize(h->d2h_stream));
+	h->slot_used[0] = h->slot_used[1] = false;
 	for (Pending *p : h->pending) delete p;
 	h->pending.clear();
 	h->carry = h->staged = 0;

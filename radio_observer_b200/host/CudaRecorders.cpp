@@ -342,34 +342,60 @@ void CudaBolidRecorder::write(Snapshot snapshot)
 
 void CudaBolidRecorder::writeRaw(Snapshot snapshot)
 {
-	// The reference's writeRaw (src/WaterfallBackend.cpp:214-267) reads rawBuffer_->at(start + y), y <
-	// length, with start = fftMarkToRaw(snapshot.start) and length = fftSamplesToRaw(snapshot.length)
-	// (Recorder's variant: the int-truncated row rate, src/WaterfallBackend.h:84-87).  Those samples are
-	// copied out of the backend's own store into a ring of just that size, at the indices writeRaw
-	// will ask for, and the reference's method writes the file from it.
-	// (Recorder::fftMarkToRaw is declared inline but defined in the reference's own translation unit)
-	const int start  = rawHandles_->at(wrap(snapshot.start, rawHandles_->size())).mark;
-	const int length = fftSamplesToRaw(snapshot.length);
-	if (length > 0 && cuda_->rawCapacity() > 0) {
-		FFTBackend::IQBuffer cut;
-		cut.resize(2, 1024 * 1024, length);
-		std::vector<float> flat(2 * (size_t)length);
-		cuda_->copyRaw(start, length, &flat[0]);
-		for (int y = 0; y < length; y++) {
-			float *dst = cut.at(start + y);
-			dst[0] = flat[2 * (size_t)y];
-			dst[1] = flat[2 * (size_t)y + 1];
-		}
-		FFTBackend::IQBuffer *keep = rawBuffer_;
-		rawBuffer_ = &cut;
-		{
-			MutexLock lock(&g_timeFormat);
-			SnapshotRecorder::writeRaw(snapshot);
-		}
-		rawBuffer_ = keep;
-	} else {
+	// SnapshotRecorder::writeRaw (src/WaterfallBackend.cpp:214-267) card for card, with the pixels handed
+	// to the FITS writer in ONE call.  The reference fetches and writes a raw-I/Q image one sample (two
+	// floats) at a time -- rawBuffer_->at(start + y), then fits_write_pix -- a million calls per bolid; a
+	// 30 min station recording has 300 of them and 3.2 GB of raw-I/Q files, and behind a backend that
+	// needs 2 s for its DSP the writer thread was the whole run time (12 s).  Same file, byte for byte:
+	// start = fftMarkToRaw(snapshot.start), length = fftSamplesToRaw(snapshot.length) with Recorder's
+	// int-truncated row rate (src/WaterfallBackend.h:84-87), samples from the backend's own store.
+	if (cuda_->rawCapacity() <= 0) {            // the reference's raw ring is in use (a recorder of unknown type is attached)
 		MutexLock lock(&g_timeFormat);
 		SnapshotRecorder::writeRaw(snapshot);
+		cuda_->noteWritten(this, snapshot.start);
+		return;
+	}
+	// (Recorder::fftMarkToRaw / fftMarkToTime are declared inline but defined in the reference's own translation unit)
+	const RawDataHandle &handle = rawHandles_->at(wrap(snapshot.start, rawHandles_->size()));
+	const int start  = handle.mark;
+	const int length = fftSamplesToRaw(snapshot.length);
+	WFTime time = handle.time;
+	std::vector<float> pixels(2 * (size_t)(length > 0 ? length : 0));
+	if (length > 0) cuda_->copyRaw(start, length, &pixels[0]);
+	{
+		MutexLock lock(&g_timeFormat);
+		string origin = backend_->getOrigin();
+		float sampleRate = (float)backend_->getStreamInfo().sampleRate;
+
+		string fileName = "!";
+		fileName += Path::join(outputDir_, getFileName("raws", "fits", time));
+		LOG_INFO("Writing raw snapshot \"" << (fileName.c_str() + 1) << "\"...");
+
+		FITSWriter w;
+		if (w.open(fileName.c_str())) {
+			w.createImage(2, length, FLOAT_IMG);
+			writeHeader(&w);
+			w.writeHeader("ORIGIN", origin.c_str(), "");
+			w.date();
+			w.comment(WFTime::now().format("Local time: %Y-%m-%d %H:%M:%S %Z", true).c_str());
+			w.writeHeader("DATE-OBS", time.format("%Y-%m-%dT%H:%M:%S").c_str(), "observation date (UTC)");
+
+			w.writeHeader("CTYPE2", "TIME", "in seconds");
+			w.writeHeader("CRPIX2", 1, "");
+			w.writeHeader("CRVAL2", (long long)time.toMilliseconds(), "unix time of the first IQ sample in this file in ms");
+			w.writeHeader("CDELT2", ((float)MS_IN_SECOND) / (float)sampleRate, "time difference between two IQ samples in ms");
+
+			w.writeHeader("CTYPE1", "CHAN", "in Hz");
+			w.writeHeader("CRPIX1", 1.f, "");
+			w.writeHeader("CRVAL1", 0, "");
+			w.writeHeader("CDELT1", 1, "");
+			w.checkStatus("Error occured while writing FITS file header.");
+
+			if (length > 0) w.write(0, length, &pixels[0]);
+			w.checkStatus("Error occured while writing data to a FITS file.");
+			w.close();
+			LOG_DEBUG("Finished writing raw snapshot.");
+		}
 	}
 	cuda_->noteWritten(this, snapshot.start);
 }

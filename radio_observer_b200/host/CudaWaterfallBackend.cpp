@@ -199,9 +199,10 @@ void CudaWaterfallBackend::startStream(StreamInfo info)
 		bolids_[0]->useGpuRecords(true);
 	}
 
-	// the Pipeline's frontends hand over vector<Complex>; a narrow frontend switches the format with
-	// its first processRaw()
-	createHandle(RO_IN_COMPLEX64);
+	// the handle is created by the first process() / processRaw(): the Pipeline's frontends hand over
+	// vector<Complex>, a narrow frontend int16, and the device work space depends on the encoding
+	if (wf_) { ro_wf_destroy(wf_); wf_ = NULL; }
+	inFormat_ = -1;
 }
 
 
@@ -260,7 +261,7 @@ bool CudaWaterfallBackend::createHandle(int inFormat)
 
 bool CudaWaterfallBackend::ensureFormat(int inFormat)
 {
-	if (inFormat_ == inFormat) return true;
+	if (inFormat_ == inFormat && wf_) return true;
 	if (samplesIn_ > 0) {
 		// one stream, one encoding: the device-side sample ring holds what was pushed so far
 		LOG_ERROR("CudaWaterfallBackend: process() and processRaw() mixed within one stream");
@@ -373,7 +374,7 @@ void CudaWaterfallBackend::pushSamples(const S *src, int count, WFTime timeOffse
 
 void CudaWaterfallBackend::process(const std::vector<Complex> &data, DataInfo info)
 {
-	if (failed_ || !wf_ || data.empty()) return;
+	if (failed_ || data.empty()) return;
 	if (!ensureFormat(RO_IN_COMPLEX64)) return;
 	procWatch_.start();
 	processSamples(&(data[0]), (int)data.size(), info);
@@ -384,7 +385,7 @@ void CudaWaterfallBackend::process(const std::vector<Complex> &data, DataInfo in
 
 void CudaWaterfallBackend::processRaw(const int16_t *iq, int count, DataInfo info)
 {
-	if (failed_ || !wf_ || count <= 0) return;
+	if (failed_ || count <= 0) return;
 	if (!ensureFormat(RO_IN_INT16)) return;
 	procWatch_.start();
 	processSamples(iq, count, info);
@@ -536,6 +537,10 @@ void CudaWaterfallBackend::waitForWriters(long firstNeededRow)
 	while (oldestLiveRow() < firstNeededRow) {
 		usleep(100);
 		waited += 100;
+		if (waited == 2L * 1000 * 1000)
+			LOG_WARNING("CudaWaterfallBackend: waiting for a recorder to write the snapshot that starts at row "
+			            << oldestLiveRow() << " (row " << delivered_ << " is next; rows below " << firstNeededRow
+			            << " are about to be overwritten)");
 		if (waited > 60L * 1000 * 1000) {
 			LOG_WARNING("CudaWaterfallBackend: a recorder has not written a snapshot for 60 s; overwriting its rows");
 			break;

@@ -1,8 +1,8 @@
 /*
  * host/shims/fitsio_min.cpp -- see fitsio.h.  A streaming writer: header cards are collected until
  * the first pixel arrives, then the padded header goes to the file and every fits_write_pix call is
- * byte-swapped through a small buffer and written at its own file offset; closing pads the data
- * unit to a whole 2880-byte block.  Nothing but the header is held in memory (the reference's
+ * byte-swapped through a small buffer and written at its own file offset (without a seek when it
+ * continues the previous one); closing pads the data unit to a whole 2880-byte block.  Nothing but the header is held in memory (the reference's
  * snapshots reach 100 MB).
  *
  * Cards follow the FITS fixed format the way CFITSIO fills them: keyword in columns 1-8, "= ",
@@ -65,6 +65,7 @@ struct ro_min_fits {
 	int bitpix;
 	long width, height;
 	size_t data_start;
+	long   at;                     // file position after the last write, -1 = unknown
 	std::vector<unsigned char> swap;
 
 	bool flush_header()
@@ -74,6 +75,7 @@ struct ro_min_fits {
 		h.resize((h.size() + BLOCK - 1) / BLOCK * BLOCK, ' ');
 		data_start = h.size();
 		header_on_disk = true;
+		at = (long)h.size();
 		return fseek(fp, 0, SEEK_SET) == 0 && fwrite(h.data(), 1, h.size(), fp) == h.size();
 	}
 };
@@ -98,6 +100,7 @@ extern "C" int fits_create_file(fitsfile **fptr, const char *filename, int *stat
 	f->bitpix = 0;
 	f->width = f->height = 0;
 	f->data_start = 0;
+	f->at = -1;
 	*fptr = f;
 	return *status;
 }
@@ -183,13 +186,24 @@ extern "C" int fits_write_pix(fitsfile *f, int datatype, long *firstpix, long lo
 	const long long first = (firstpix[0] - 1) + (firstpix[1] - 1) * (long long)f->width;
 	if (first < 0 || nelem < 0 || first + nelem > (long long)f->width * f->height) return *status = WRITE_ERROR;
 	if (!f->flush_header()) return *status = WRITE_ERROR;
-	f->swap.resize((size_t)nelem * esz);
+	const size_t bytes = (size_t)nelem * esz;
+	if (f->swap.size() < bytes) f->swap.resize(bytes);
 	const unsigned char *src = (const unsigned char *)array;
-	for (long long i = 0; i < nelem; i++)
-		for (int b = 0; b < esz; b++) f->swap[(size_t)i * esz + b] = src[(size_t)i * esz + (esz - 1 - b)];
-	if (fseek(f->fp, (long)(f->data_start + (size_t)first * esz), SEEK_SET) != 0 ||
-	    fwrite(f->swap.data(), 1, f->swap.size(), f->fp) != f->swap.size())
-		return *status = WRITE_ERROR;
+	unsigned char *dst = f->swap.data();
+	if (esz == 4) {
+		for (long long i = 0; i < nelem; i++) {
+			dst[4 * i] = src[4 * i + 3]; dst[4 * i + 1] = src[4 * i + 2];
+			dst[4 * i + 2] = src[4 * i + 1]; dst[4 * i + 3] = src[4 * i];
+		}
+	} else {
+		for (long long i = 0; i < nelem; i++) { dst[2 * i] = src[2 * i + 1]; dst[2 * i + 1] = src[2 * i]; }
+	}
+	// the reference writes a raw-I/Q image one sample (8 bytes) per call, a million calls per file: a
+	// write that continues where the last one ended goes to stdio's buffer without a seek (fseek flushes)
+	const long where = (long)(f->data_start + (size_t)first * esz);
+	if (where != f->at && fseek(f->fp, where, SEEK_SET) != 0) return *status = WRITE_ERROR;
+	if (fwrite(f->swap.data(), 1, bytes, f->fp) != bytes) { f->at = -1; return *status = WRITE_ERROR; }
+	f->at = where + (long)bytes;
 	return *status;
 }
 
