@@ -38,6 +38,7 @@ def main():
     ap.add_argument("--dir", default="/dev/shm" if os.path.isdir("/dev/shm") else "/tmp")
     ap.add_argument("--out", default=None, help="write the snapshot / bolid FITS files and the metadata CSV here")
     ap.add_argument("--max-files", type=int, default=200, help="bound on FITS files written per recorder")
+    ap.add_argument("--keep-archive", action="store_true", help="reuse an archive file of the same length and leave it behind")
     ap.add_argument("--chunk-frames", type=int, default=16384, help="frames per pinned staging buffer")
     ap.add_argument("--copy-threads", type=int, default=4, help="threads copying the archive into the staging buffer")
     a = ap.parse_args()
@@ -52,7 +53,7 @@ def main():
     path = os.path.join(a.dir, "ro_archive_%dh.npy" % int(a.hours * 100))
     n_total = int(a.hours * 3600 * SR)
     t_gen = 0.0
-    if rank == 0:
+    if rank == 0 and not (a.keep_archive and os.path.exists(path)):
         t0 = time.time()
         base = synth.generate_int16(synth.SynthSpec(sample_rate=SR, n_samples=600 * SR, seed=4, carrier_freq=26700.3,
                                                     meteor_band=(26450.0, 26550.0)))
@@ -139,10 +140,17 @@ def main():
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
-        try:
-            os.remove(path)
-        except OSError:
-            pass
+        for f in [path] if not a.keep_archive else []:
+            try:
+                os.remove(f)
+            except OSError:
+                pass
+        for f in os.listdir(a.dir):            # the merged arrays of reprocess_archive
+            if f.startswith("ro_rows_") or f.startswith("ro_det_"):
+                try:
+                    os.remove(os.path.join(a.dir, f))
+                except OSError:
+                    pass
     return 0
 
 

@@ -8,7 +8,9 @@ import subprocess
 import sys
 
 KEEP = [r"^Kernel Name$", r"^Block Size$", r"^Grid Size$", r"^gpu__time_duration\.sum$", r"^dram__bytes_(read|write)\.sum$",
-        r"^dram__throughput\.avg\.pct_of_peak_sustained_elapsed$",
+        r"^dram__throughput\.avg\.pct_of_peak_sustained_elapsed$", r"^gpu__dram_throughput\.avg\.pct_of_peak_sustained_elapsed$",
+        r"^lts__t_sector_hit_rate\.pct$", r"^l1tex__m_xbar2l1tex_read_bytes\.sum$", r"^l1tex__m_l1tex2xbar_write_bytes\.sum$",
+        r"^sm__cycles_elapsed\.max$", r"^launch__occupancy_limit_(registers|shared_mem|warps)$", r"^sm__warps_active\.avg\.pct_of_peak_sustained_active$",
         r"^(lts|l1tex|sm)__throughput\.avg\.pct_of_peak_sustained_elapsed$", r"^smsp__issue_active\.avg\.per_cycle_active$",
         r"^sm__pipe_(fma|fmaheavy|alu)_cycles_active\.avg\.pct_of_peak_sustained_elapsed$",
         r"^sm__inst_executed_pipe_(xu|lsu)\.avg\.pct_of_peak_sustained_elapsed$", r"^smsp__inst_executed\.sum$",
