@@ -216,8 +216,39 @@ def staged_compute(bins: int, overlap: int, sample_rate: int, bands: Sequence[Tu
     chunk_samples = (chunk_frames - 1) * hop + bins
     stage = [PinnedArray((2 * chunk_samples,), np.int16) for _ in range(2)]
 
-    def fill(buf: np.ndarray, src: np.ndarray):
-        n = src.shape[0]
+    def fill(buf: np.ndarray, iq_map: np.ndarray, e0: int, e1: int):
+        """buf[:e1 - e0] = iq_map[e0:e1] (int16 elements).  A numpy memmap of a file is read with
+        os.preadv straight into the pinned buffer, one slice per thread: copying out of the mapping
+        instead takes a minor page fault per 4 KB under the process-wide mm lock and stays at the speed
+        of one thread (23 GB/s measured on the B200 box, whatever the thread count)."""
+        n = e1 - e0
+        fn = getattr(iq_map, "filename", None)
+        if isinstance(iq_map, np.memmap) and fn is not None and iq_map.dtype == np.int16 and iq_map.ndim == 1:
+            base = int(iq_map.offset) + 2 * e0
+            nbytes = 2 * n
+            raw = memoryview(buf).cast("B")
+            parts = max(1, copy_threads)
+            step = -(-nbytes // parts)
+            step += (-step) % 4096
+
+            def rd(a):
+                fd = os.open(fn, os.O_RDONLY)
+                try:
+                    at, end = a, min(nbytes, a + step)
+                    while at < end:
+                        got = os.preadv(fd, [raw[at:end]], base + at)
+                        if got <= 0:
+                            raise IOError("short read from %s" % fn)
+                        at += got
+                finally:
+                    os.close(fd)
+            ths = [threading.Thread(target=rd, args=(a,)) for a in range(0, nbytes, step)]
+            for t in ths:
+                t.start()
+            for t in ths:
+                t.join()
+            return
+        src = iq_map[e0:e1]
         if copy_threads <= 1 or n < (1 << 22):
             buf[:n] = src
             return
@@ -242,7 +273,7 @@ def staged_compute(bins: int, overlap: int, sample_rate: int, bands: Sequence[Tu
 
         def load(i):
             f0, f1, s0, s1 = spans[i]
-            fill(stage[i & 1].array, iq_map[2 * s0:2 * s1])
+            fill(stage[i & 1].array, iq_map, 2 * s0, 2 * s1)
         load(0)
         for i, (f0, f1, s0, s1) in enumerate(spans):
             if i + 1 < len(spans):

@@ -40,9 +40,12 @@ def main():
     ap.add_argument("--max-files", type=int, default=200, help="bound on FITS files written per recorder")
     ap.add_argument("--keep-archive", action="store_true", help="reuse an archive file of the same length and leave it behind")
     ap.add_argument("--chunk-frames", type=int, default=16384, help="frames per pinned staging buffer")
-    ap.add_argument("--copy-threads", type=int, default=4, help="threads copying the archive into the staging buffer")
+    ap.add_argument("--copy-threads", type=int, default=0,
+                    help="threads reading the archive into the staging buffer (0 = min(8, cores / ranks))")
     a = ap.parse_args()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    if a.copy_threads <= 0:
+        a.copy_threads = max(2, min(8, (os.cpu_count() or 8) // world))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     out_fd = os.dup(1)
     os.dup2(2, 1)
