@@ -13,7 +13,7 @@ from typing import Optional, Sequence, Tuple
 import numpy as np
 
 PREC_FP32, PREC_FP64 = 0, 1
-TUNE_NO_FUSED, TUNE_NO_PAIR = 1, 2
+TUNE_NO_FUSED, TUNE_NO_PAIR, TUNE_NO_CHAIN = 1, 2, 4
 IN_INT16, IN_FLOAT32, IN_COMPLEX64 = 0, 1, 2
 MAX_BANDS = 4
 

@@ -645,6 +645,7 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 	// 8k kernel (two 256-thread CTAs per SM): chaining passes 2 and 3 gives 43.5 -> 47.2 M frames/s;
 	// the 4k kernel (three CTAs per SM) gains nothing
 	h->stagger_small = h->log2n == 13 ? 6 : 0;
+	if (cfg->tuning & RO_TUNE_NO_CHAIN) h->stagger = h->stagger_small = 0;
 	int log2nb = 14;                              // in-CTA transform of the split path
 	if (h->log2n - log2nb > 5) log2nb = h->log2n - 5;      // the split kernel does radix <= 32
 	if (h->log2n > 14 && ro::v2_pick(log2nb, ro::V2_SPLIT, false, &h->v2s)) {

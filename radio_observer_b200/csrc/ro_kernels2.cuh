@@ -155,7 +155,7 @@ template <int LOG2N, int P, int R3, int MODE>
 constexpr size_t wf2_smem_bytes()
 {
 	constexpr size_t N = (size_t)1 << LOG2N;
-	constexpr size_t PAD1 = (R3 < 16) ? R3 : 0;
+	constexpr size_t PAD1 = (R3 < 16 && !(R3 == 8 && P == 32)) ? R3 : 0;   // 8k: swizzled instead of padded, see the kernel
 	return sizeof(c64) * (N + P * PAD1) + (mode_is_split(MODE) ? 0 : sizeof(float) * (N / 2)) + 32 +
 	       (MODE == MODE_STAGED ? 4 * N : 0) + (mode_is_split(MODE) && P / R3 >= 2 ? 4 * N : 0) +
 	       (mode_is_fused(MODE) ? FUSED_RING_BYTES + FUSED_BAR_BYTES : 0);
@@ -188,7 +188,13 @@ wf_fft2_kernel(const Wf2Params p)
 	constexpr int M = N / R1;                  // = R2*R3
 	static_assert(R1 * R2 * R3 == N, "factorisation");
 	static_assert(R3 <= 16 && R3 >= 2 && P % R3 == 0, "R3");
-	constexpr int PAD1 = (R3 < 16) ? R3 : 0;
+	// Pass 2 reads row k1 of S with the R3 lanes (k1, n3): a half-warp covers 16 / R3 rows, which must fall
+	// into different banks.  R3 = 16: one row per half-warp.  R3 = 4: rows padded by R3 elements.  R3 = 8:
+	// bit 3 of the position inside the row is XORed with the row's parity instead -- the 2 KB of padding
+	// were what kept the 8k kernel at ONE CTA per SM (116 768 B of shared memory each, ncu
+	// launch__occupancy_limit_shared_mem = 1; 114 720 B fit twice).
+	constexpr bool SWZ1 = R3 == 8 && P == 32;        // the 2k kernel (P = 16) is not short of shared memory: padded, 1.7 % faster
+	constexpr int PAD1 = (R3 < 16 && !SWZ1) ? R3 : 0;
 	constexpr int ROW1 = M + PAD1;
 	constexpr int LP = ilog2(P);
 	constexpr int L3 = ilog2(R3);
@@ -484,7 +490,7 @@ wf_fft2_kernel(const Wf2Params p)
 		// S still holds the previous frame's pass-3 inputs until every thread has read them
 		if (f > f0) mbar_wait(bar_rd3, (unsigned int)(f - 1 - f0) & 1u);
 #pragma unroll
-		for (int k1 = 0; k1 < R1; k1++) S[k1 * ROW1 + t] = v[bitrev(k1, LP)];
+		for (int k1 = 0; k1 < R1; k1++) S[k1 * ROW1 + ((SWZ1 && (k1 & 1)) ? (t ^ 8) : t)] = v[bitrev(k1, LP)];
 		__syncthreads();
 		if constexpr (FUSED) {
 			// every warp is through the load phase of this frame: the ring's own stages can take the first
@@ -519,7 +525,11 @@ wf_fft2_kernel(const Wf2Params p)
 			const int k1 = t / R3, n3 = t % R3;
 			if (CHAIN && (p.stagger & 2)) chain_wait(wq, wl, cdist);
 #pragma unroll
-			for (int n2 = 0; n2 < R2; n2++) v[n2] = S[k1 * ROW1 + n2 * R3 + n3];
+			for (int n2 = 0; n2 < R2; n2++) {
+				// SWZ1: (n2*8 + n3) ^ (8*(k1 & 1)) = n2*8 + n3 +- 8*(k1 & 1), the sign by the parity of n2
+				const int sw = SWZ1 ? ((k1 & 1) << 3) : 0;
+				v[n2] = S[k1 * ROW1 + n2 * R3 + n3 + ((n2 & 1) ? -sw : sw)];
+			}
 			if (CHAIN && (p.stagger & 2)) chain_pass(wq, wl, LEVELS, cdist);
 			mbar_arrive(bar_rd2);                       // my pass-2 inputs are in registers
 			fft_fwd2<R2, USE_DIT>(v);

@@ -27,6 +27,7 @@ def main():
     ap.add_argument("--lo", type=int, default=10)
     ap.add_argument("--hi", type=int, default=16)
     ap.add_argument("--fmt", default="int16", choices=["int16", "float32"])
+    ap.add_argument("--tuning", type=int, default=0, help="ro_wf_config.tuning bits (A/B switches)")
     a = ap.parse_args()
     peak = 6650.0
     pp = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -46,7 +47,7 @@ def main():
     for lg in range(a.lo, a.hi + 1):
         N = 1 << lg
         for ov in (0, N // 2, 3 * N // 4):
-            wf = ro.Waterfall(N, ov, sample_rate=96000, in_format=fmt)
+            wf = ro.Waterfall(N, ov, sample_rate=96000, in_format=fmt, tuning=a.tuning)
             F = wf.frame_count(S)
             wf.process_resident(d_iq.ptr, S, d_rows.ptr, None, sync=True)          # warm-up
             wf.set_profiling(True)
