@@ -119,6 +119,22 @@ __device__ __forceinline__ void chain_pass(int q, int l, int levels, int dist = 
 {
 	if (l + dist < levels) asm volatile("bar.arrive %0, 64;" :: "r"(3 * q + l + dist) : "memory");
 }
+// Arrival on a split barrier ("my inputs of this pass are in registers"), every thread for itself.
+// -DRO_WARP_ARRIVE=1 lets lane 0 arrive for its warp after a __syncwarp() (16 arrivals instead of 512 on
+// one mbarrier): measured SLOWER on B200 at every size (16k 26.6 -> 25.7, 8k 51.2 -> 46.5, 1k 426 -> 403
+// M frames/s): the __syncwarp() costs more than the arrivals, which the hardware evidently combines.
+#ifndef RO_WARP_ARRIVE
+#define RO_WARP_ARRIVE 0
+#endif
+__device__ __forceinline__ void split_arrive(unsigned long long *bar, int t)
+{
+	if (RO_WARP_ARRIVE) {
+		__syncwarp();
+		if ((t & 31) == 0) mbar_arrive(bar);
+	} else {
+		mbar_arrive(bar);
+	}
+}
 // A fence for ptxas.  Nothing at run time (`never` is a kernel parameter that is always 0; if it
 // ever ran it would be a warp-wide barrier on id 15, which is harmless), but a barrier instruction
 // in the stream keeps ptxas from interleaving a load burst with the arithmetic around it.  Found by
@@ -224,8 +240,8 @@ wf_fft2_kernel(const Wf2Params p)
 
 	if (t == 0) {
 		mbar_init(mbar, 1);
-		mbar_init(bar_rd2, T);
-		mbar_init(bar_rd3, T);
+		mbar_init(bar_rd2, RO_WARP_ARRIVE ? T / 32 : T);
+		mbar_init(bar_rd3, RO_WARP_ARRIVE ? T / 32 : T);
 	}
 	for (int i = t; i < WINF; i += T) win[i] = __ldg(p.window_half + i);
 	__syncthreads();
@@ -531,7 +547,7 @@ wf_fft2_kernel(const Wf2Params p)
 				v[n2] = S[k1 * ROW1 + n2 * R3 + n3 + ((n2 & 1) ? -sw : sw)];
 			}
 			if (CHAIN && (p.stagger & 2)) chain_pass(wq, wl, LEVELS, cdist);
-			mbar_arrive(bar_rd2);                       // my pass-2 inputs are in registers
+			split_arrive(bar_rd2, t);                   // my pass-2 inputs are in registers
 			fft_fwd2<R2, USE_DIT>(v);
 			RO_SITE(2, p.stagger & 1);
 			twiddle_powers2<R2>(v, b2);
@@ -568,7 +584,7 @@ wf_fft2_kernel(const Wf2Params p)
 				}
 			}
 			if (CHAIN && (p.stagger & 4)) chain_pass(wq, wl, LEVELS, cdist3);
-			mbar_arrive(bar_rd3);                      // my pass-3 inputs are in registers
+			split_arrive(bar_rd3, t);                  // my pass-3 inputs are in registers
 			float mag[R3][G];
 #pragma unroll
 			for (int c = 0; c < G; c++) {
@@ -670,7 +686,7 @@ wf_fft2_kernel(const Wf2Params p)
 			c64 u[R3];
 #pragma unroll
 			for (int n3 = 0; n3 < R3; n3++) u[n3] = S[((t / R1) * R3 + n3) * R1 + ((t % R1) ^ (n3 * SW))];
-			mbar_arrive(bar_rd3);
+			split_arrive(bar_rd3, t);
 			fft_fwd2<R3, USE_DIT>(u);
 #pragma unroll
 			for (int k3 = 0; k3 < R3; k3++) {
