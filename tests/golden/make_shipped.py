@@ -10,7 +10,9 @@ The three station configurations the reference ships, run end to end through the
                           directory OUT, "snapshot_length" -> 20 (so that two minutes of input give five
                           snapshots; the FFT, band and detector keys are untouched)
   shipped/<name>/         meta.json (input recipe + sha256, row count), rowinfo.npy, npa.npy, bolid.txt,
-                          fits.json (every file: cards, shape, sha256 of the pixels),
+                          fits.json (every file: cards, shape, sha256 of the pixels; raw-I/Q files also
+                          first_sample (its place in the input),
+                          head_rows and the sha256 of that many leading samples),
                           band_rows.npy (the snapshot band of every 8th row)
 
 Run in the build container:  make -C oracle ref && python tests/golden/make_shipped.py
@@ -35,6 +37,8 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, HERE)
 from radio_observer_b200 import synth  # noqa: E402
 from make_golden import read_fits      # noqa: E402
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from helpers import raws_head_rows     # noqa: E402
 
 REFERENCE = "/root/reference"
 REF = os.path.join(ROOT, "oracle", "_ref", "ref_oracle")
@@ -112,6 +116,13 @@ def run_reference(binary, cfg_text, iq, sr, tmp, flags=(), dump_rows=True):
     return dict(rows=rows, info=info, npa=npa, bolid=bolid, fits=fits, csv=csv, timing=timing, stderr=r.stderr)
 
 
+def _card_value(cards, key):
+    for card in cards:
+        if card.startswith(key.ljust(8) + "="):
+            return card.split("=", 1)[1].split("/")[0].strip()
+    raise KeyError(key)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     for name, c in CASES.items():
@@ -133,6 +144,18 @@ def main():
         open(os.path.join(d, "bolid.txt"), "w").write(r["bolid"])
         fits = {fn: dict(cards=f["cards"], shape=f["shape"], sha256=hashlib.sha256(f["data"].tobytes()).hexdigest())
                 for fn, f in r["fits"].items()}
+        # raw-I/Q files: the tail is read ahead of the producer (helpers.raws_head_rows), so the part that is
+        # a fixed function of the input gets its own hash; the full hash above is of a run whose tail was
+        # complete (checked: the file is the input, sample for sample)
+        for fn, f in r["fits"].items():
+            if fn.endswith("_raws.fits"):
+                head = raws_head_rows(f["shape"][1], c["sr"], c["bins"], c["overlap"])
+                px = f["data"].reshape(-1, 2)
+                src = iq.reshape(-1, 2).astype(np.float32)
+                t = int(_card_value(f["cards"], "CRVAL2")) * c["sr"] // 1000
+                at = [k for k in range(max(0, t - 2 * c["bins"]), t + 2 * c["bins"]) if np.array_equal(src[k:k + 64], px[:64])]
+                assert len(at) == 1 and np.array_equal(src[at[0]:at[0] + len(px)], px), "%s: tail not complete, run again" % fn
+                fits[fn].update(first_sample=at[0], head_rows=head, sha256_head=hashlib.sha256(px[:head].tobytes()).hexdigest())
         json.dump(fits, open(os.path.join(d, "fits.json"), "w"), indent=1)
         # the snapshot band of every 8th row (bins from the first snap file's NAXIS1 and the config's low_freq)
         snap = [f for fn, f in r["fits"].items() if fn.endswith("_snap.fits") and f["shape"][0] < c["bins"]]

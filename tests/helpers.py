@@ -144,3 +144,36 @@ def classify_det_mismatch(ref_rows, d, gpu_det, ref_npa):
             else:
                 n_bad += 1
     return n_exact, n_tie, n_bad
+
+
+# ----------------------------------------------------------------------------
+# raw-I/Q snapshot files: the part that does not depend on thread timing
+# ----------------------------------------------------------------------------
+def raws_head_rows(naxis2, sr, bins, overlap):
+    """Leading samples of a `raws` file that were in the raw ring when the snapshot was queued.
+
+    SnapshotRecorder::writeRaw (reference src/WaterfallBackend.cpp:214-267) reads fftSamplesToRaw(rows)
+    samples, and the recorder's getFFTSampleRate() is an `int` (src/WaterfallBackend.h:77-87): 5.859
+    rows/s becomes 5, so a 65-row snapshot asks for 13 s of samples where the rows span 11.1 s.  The
+    tail lies AHEAD of the producer when the snapshot is queued; the writer thread gets there later and
+    finds whatever the producer has pushed by then -- the samples, or the ring's initial zeros.  Seen in
+    the stock reference under load (first zero row 1146879 .. 1263886 of 1.2-1.3 M), so only the head is
+    a fixed function of the input."""
+    hop = bins - overlap
+    rate = int(sr / hop)
+    rows = int(round(naxis2 * rate / float(sr))) if rate > 0 else 0
+    return max(0, min(int(naxis2), (rows - 1) * hop))
+
+
+def assert_raws_equal(a, b, head, what=""):
+    """Two `raws` images ([NAXIS2, 2] float32, any shape with 2 values per sample): identical over the
+    head; past it a sample may differ only where one side has not been written yet (0, 0)."""
+    a = np.asarray(a).reshape(-1, 2)
+    b = np.asarray(b).reshape(-1, 2)
+    assert a.shape == b.shape, (what, a.shape, b.shape)
+    assert np.array_equal(a[:head], b[:head]), "%s: raw samples differ inside the first %d" % (what, head)
+    diff = np.nonzero((a[head:] != b[head:]).any(axis=1))[0]
+    if len(diff):
+        unwritten = (a[head:][diff] == 0).all(axis=1) | (b[head:][diff] == 0).all(axis=1)
+        assert unwritten.all(), "%s: %d raw samples past the head differ and neither side is unwritten" % (what, int((~unwritten).sum()))
+    return len(diff)
