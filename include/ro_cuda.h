@@ -164,6 +164,37 @@ int  ro_wf_process_host(ro_wf *h, const void *iq, size_t n_samples,
                         float *rows, ro_det_rec *det,
                         size_t max_frames, size_t *n_frames);
 
+/* ---- allocation-free variant --------------------------------------------- */
+
+/* NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  The long-frame transform of ro_wf_process_resident -- wf_split_kernel into a scratch, then
+ * wf_fft2_kernel<14,32,16,MODE_SPLIT> out of it -- with that scratch and the window / twiddle
+ * tables in file-scope __device__ arrays of the library (radio_observer_b200/csrc/ro_static.cu)
+ * instead of a handle's cudaMalloc'ed buffers.  No handle, and no cudaMalloc, cudaFree or other
+ * allocating routine on this path: the first call on a device looks the arrays' addresses up and
+ * the first call for a frame size copies its tables (1.7 MB at most) into them; after that a call
+ * is two kernel launches.
+ *
+ *   bins       a power of two, 32768 .. RO_STATIC_MAX_BINS
+ *   overlap, in_format (RO_IN_INT16 | RO_IN_FLOAT32), iq_gain: as in ro_wf_config
+ *   d_iq       n_samples complex samples in device memory (float32: 8-byte aligned)
+ *   d_rows     receives min(frame count, max_frames) FULL rows of `bins` floats, fftshifted
+ *              magnitudes, pitch `bins` (16-byte aligned); *n_frames = rows written
+ *   cuda_stream  the caller's cudaStream_t (NULL = the default stream); sync != 0 waits for it
+ *
+ * Limit: frames * 8 * bins <= RO_STATIC_SCRATCH_BYTES per call (256 / 128 / 64 frames of 32k / 64k /
+ * 128k); more is RO_E_INVALID with the numbers in ro_last_error(), and nothing is launched.  Every
+ * GPU that runs this entry point holds the arrays (RO_STATIC_SCRATCH_BYTES + 1.7 MB) until the
+ * process exits.  ALL calls on a device share them: calls that overlap on the GPU (two streams, two
+ * threads) race; issue them on one stream or wait in between.  The scratch keeps the last call's
+ * contents and needs no clearing (every element is written before it is read). */
+#define RO_STATIC_SCRATCH_BYTES (64u << 20)
+#define RO_STATIC_MAX_BINS      131072
+int  ro_wf_long_rows_static(int32_t device, int32_t bins, int32_t overlap, int32_t in_format,
+                            double iq_gain, const void *d_iq, size_t n_samples, float *d_rows,
+                            size_t max_frames, size_t *n_frames, void *cuda_stream, int sync);
+
 /* ---- stage variants (unit tests, ncu attribution) ------------------------ */
 
 /* Only the reduction kernel (row_avg x bin_decim of the handle): n_in full rows of `bins` floats

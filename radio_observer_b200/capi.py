@@ -80,6 +80,7 @@ def load_library():
         "ro_wf_sync": (C.c_int, [vp]),
         "ro_wf_set_profiling": (C.c_int, [vp, C.c_int]),
         "ro_wf_kernel_name": (C.c_char_p, [vp]),
+        "ro_wf_long_rows_static": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_double, vp, sz, vp, sz, P(sz), vp, C.c_int]),
         "ro_wf_kernel_times": (C.c_int, [vp, P(C.c_double), P(u64)]),
         "ro_wf_launch_count": (u64, [vp]),
         "ro_dev_count": (C.c_int, [P(C.c_int)]),
@@ -124,6 +125,21 @@ def twiddle_table(n: int) -> np.ndarray:
 def device_count() -> int:
     n = C.c_int(0)
     _check(load_library().ro_dev_count(C.byref(n)))
+    return n.value
+
+
+STATIC_SCRATCH_BYTES = 64 << 20        # RO_STATIC_SCRATCH_BYTES
+STATIC_MAX_BINS = 131072               # RO_STATIC_MAX_BINS
+
+
+def long_rows_static(device: int, bins: int, overlap: int, in_format: int, iq_gain: float, d_iq: int,
+                     n_samples: int, d_rows: int, max_frames: int, cuda_stream: Optional[int] = None,
+                     sync: bool = True) -> int:
+    """ro_wf_long_rows_static: the long-frame transform on the library's static device arrays (no
+    handle, no allocation).  Device pointers as integers; returns the number of rows written."""
+    n = C.c_size_t(0)
+    _check(load_library().ro_wf_long_rows_static(device, bins, overlap, in_format, float(iq_gain), d_iq, n_samples,
+                                                 d_rows, max_frames, C.byref(n), cuda_stream, 1 if sync else 0))
     return n.value
 
 

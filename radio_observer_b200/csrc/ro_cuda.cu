@@ -55,6 +55,16 @@ struct Pending {            // one submitted batch of the streaming path
 
 }  // namespace
 
+// the same for the library's other translation units (ro_static.cu)
+__attribute__((visibility("hidden"))) int ro_internal_fail(int code, const char *fmt, ...)
+{
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(g_err, sizeof g_err, fmt, ap);
+	va_end(ap);
+	return code;
+}
+
 struct ro_wf {
 	ro_wf_config cfg;
 	int N, log2n, overlap, hop, fmt;      // fmt: device encoding (int16 / float32)
