@@ -26,6 +26,26 @@
 
 namespace ro {
 
+// -DRO_TRACE=1 (tools/trace16k.py, never the product build): lane 0 of every warp of CTAs 0 and 73 of the
+// staged 16k kernel stamps clock64() at the phase boundaries of frames RO_TRACE_F0 .. +RO_TRACE_NF-1 of the CTA
+// into a file-scope array that ro_trace_dump (ro_v2.cu) copies out: the per-warp timeline of a frame.
+#ifndef RO_TRACE
+#define RO_TRACE 0
+#endif
+#if RO_TRACE
+#define RO_TRACE_F0 16
+#define RO_TRACE_NF 8
+#define RO_TRACE_NP 20
+static __device__ unsigned long long ro_trace_buf[2 * RO_TRACE_NF * 16 * RO_TRACE_NP];
+#define RO_TP(i) do { \
+	if (MODE == MODE_STAGED && LOG2N == 14 && (t & 31) == 0 && f - f0 >= RO_TRACE_F0 && f - f0 < RO_TRACE_F0 + RO_TRACE_NF && \
+	    (blockIdx.x == 0 || blockIdx.x == 73)) \
+		ro_trace_buf[(((blockIdx.x ? 1 : 0) * RO_TRACE_NF + (int)(f - f0) - RO_TRACE_F0) * 16 + (t >> 5)) * RO_TRACE_NP + (i)] = clock64(); \
+} while (0)
+#else
+#define RO_TP(i) do { } while (0)
+#endif
+
 struct Wf2Params {
 	const void   *iq;           // device input, interleaved int16 I/Q; 16-byte aligned when STAGE
 	const float  *window_half;  // w[0 .. N/2)   (w[N-1-i] == w[i])
@@ -339,8 +359,10 @@ wf_fft2_kernel(const Wf2Params p)
 		// ---- load (shared-memory ring or global) + window ----
 		if (STAGE) {
 			const int base = (int)(((f - f0) * hop) & NMASK);
+			RO_TP(0);
 			mbar_wait(mbar, parity);
 			parity ^= 1u;
+			RO_TP(1);
 			// all loads first, then the conversions, fenced on both sides (see ptxas_fence)
 			unsigned int raw[R1];
 			float wv[R1];
@@ -499,15 +521,20 @@ wf_fft2_kernel(const Wf2Params p)
 		}
 
 		// ---- pass 1 ----
+		RO_TP(2);
 		fft_fwd2<R1, USE_DIT>(v);
 		RO_SITE(0, p.stagger & 1);
 		twiddle_powers2<R1>(v, b1);
 		RO_SITE(1, p.stagger & 1);
+		RO_TP(3);
 		// S still holds the previous frame's pass-3 inputs until every thread has read them
 		if (f > f0) mbar_wait(bar_rd3, (unsigned int)(f - 1 - f0) & 1u);
+		RO_TP(4);
 #pragma unroll
 		for (int k1 = 0; k1 < R1; k1++) S[k1 * ROW1 + ((SWZ1 && (k1 & 1)) ? (t ^ 8) : t)] = v[bitrev(k1, LP)];
+		RO_TP(5);
 		__syncthreads();
+		RO_TP(6);
 		if constexpr (FUSED) {
 			// every warp is through the load phase of this frame: the ring's own stages can take the first
 			// steps of the next frame now, a whole frame ahead of their use
@@ -540,6 +567,7 @@ wf_fft2_kernel(const Wf2Params p)
 		{
 			const int k1 = t / R3, n3 = t % R3;
 			if (CHAIN && (p.stagger & 2)) chain_wait(wq, wl, cdist);
+			RO_TP(7);
 #pragma unroll
 			for (int n2 = 0; n2 < R2; n2++) {
 				// SWZ1: (n2*8 + n3) ^ (8*(k1 & 1)) = n2*8 + n3 +- 8*(k1 & 1), the sign by the parity of n2
@@ -548,18 +576,23 @@ wf_fft2_kernel(const Wf2Params p)
 			}
 			if (CHAIN && (p.stagger & 2)) chain_pass(wq, wl, LEVELS, cdist);
 			split_arrive(bar_rd2, t);                   // my pass-2 inputs are in registers
+			RO_TP(8);
 			fft_fwd2<R2, USE_DIT>(v);
 			RO_SITE(2, p.stagger & 1);
 			twiddle_powers2<R2>(v, b2);
 			RO_SITE(3, p.stagger & 1);
+			RO_TP(9);
 			mbar_wait(bar_rd2, (unsigned int)(f - f0) & 1u);   // ... and so are everyone else's
+			RO_TP(10);
 			{
 				const int col = k1 ^ (n3 * SW);
 #pragma unroll
 				for (int k2 = 0; k2 < R2; k2++) S[(k2 * R3 + n3) * R1 + col] = v[bitrev(k2, LP)];
 			}
+			RO_TP(11);
 		}
 		__syncthreads();
+		RO_TP(12);
 
 		// ---- pass 3 + magnitude + fftshift store ----
 		constexpr int G = P / R3;                  // 16-point (R3) transforms per thread
@@ -571,6 +604,7 @@ wf_fft2_kernel(const Wf2Params p)
 			const int k1b = pbase % R1, k2 = pbase / R1;
 			c64 (&u)[P] = v;                       // u[c*R3 + n3]
 			if (CHAIN && (p.stagger & 4)) chain_wait(wq, wl, cdist3);
+			RO_TP(13);
 #pragma unroll
 			for (int n3 = 0; n3 < R3; n3++) {
 				constexpr int GM = G - 1;
@@ -585,6 +619,7 @@ wf_fft2_kernel(const Wf2Params p)
 			}
 			if (CHAIN && (p.stagger & 4)) chain_pass(wq, wl, LEVELS, cdist3);
 			split_arrive(bar_rd3, t);                  // my pass-3 inputs are in registers
+			RO_TP(14);
 			float mag[R3][G];
 #pragma unroll
 			for (int c = 0; c < G; c++) {
@@ -601,6 +636,7 @@ wf_fft2_kernel(const Wf2Params p)
 				RO_SITE(4, p.stagger & 1);
 			}
 			RO_SITE(5, p.stagger & 1);
+			RO_TP(15);
 			if (SPLIT) {
 				// output k of residue class r is bin Na*k + r of the Na*N-point frame
 				const int la = p.log2na;
@@ -677,6 +713,7 @@ wf_fft2_kernel(const Wf2Params p)
 				if (G == 2) *reinterpret_cast<float2 *>(row + off) = make_float2(mag[k3][0], mag[k3][1]);
 				else *reinterpret_cast<float4 *>(row + off) = make_float4(mag[k3][0], mag[k3][1], mag[k3][2 % G], mag[k3][3 % G]);
 			}
+			RO_TP(16);
 			}
 		} else {
 			const int la = SPLIT ? p.log2na : 0;

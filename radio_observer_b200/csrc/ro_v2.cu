@@ -173,3 +173,13 @@ cudaError_t v2_launch_split(cudaStream_t s, int log2n, int log2na, bool f32in, c
 }
 
 }  // namespace ro
+
+#if RO_TRACE
+// tools/trace16k.py: the timeline the instrumented staged 16k kernel left behind (see ro_kernels2.cuh)
+extern "C" int ro_trace_dump(unsigned long long *out, size_t n)
+{
+	const size_t have = sizeof(ro::ro_trace_buf) / sizeof(unsigned long long);
+	if (n > have) n = have;
+	return (int)cudaMemcpyFromSymbol(out, ro::ro_trace_buf, n * sizeof(unsigned long long));
+}
+#endif

@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--hi", type=int, default=16)
     ap.add_argument("--fmt", default="int16", choices=["int16", "float32"])
     ap.add_argument("--tuning", type=int, default=0, help="ro_wf_config.tuning bits (A/B switches)")
+    ap.add_argument("--scratch-mb", type=int, default=0, help="ro_wf_config.scratch_mb (long-frame path), 0 = default")
     a = ap.parse_args()
     peak = 6650.0
     pp = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -47,7 +48,7 @@ def main():
     for lg in range(a.lo, a.hi + 1):
         N = 1 << lg
         for ov in (0, N // 2, 3 * N // 4):
-            wf = ro.Waterfall(N, ov, sample_rate=96000, in_format=fmt, tuning=a.tuning)
+            wf = ro.Waterfall(N, ov, sample_rate=96000, in_format=fmt, tuning=a.tuning, scratch_mb=a.scratch_mb)
             F = wf.frame_count(S)
             wf.process_resident(d_iq.ptr, S, d_rows.ptr, None, sync=True)          # warm-up
             wf.set_profiling(True)
