@@ -375,8 +375,15 @@ int launch_fft(ro_wf *h, cudaStream_t s, const void *d_iq, float *d_rows, long l
 			const long long items = nf << h->log2na;
 			const long long cap = h->v2s_grid_cap;
 			long long ipc = (items + cap - 1) / cap;                 // contiguous items per CTA
-			const int pair = (h->cfg.tuning & RO_TUNE_NO_PAIR) ? 0 : 1;
-			if (pair) ipc += ipc & 1;                                // classes r, r+1 stay in one CTA
+			int pair = (h->cfg.tuning & RO_TUNE_NO_PAIR) ? 0 : 1;
+			// Na >= 4: four classes are stored together (pair = 2) when a CTA's share is a multiple of four or long
+			// enough that rounding it up costs little; the short launches of the streaming path keep pairs
+			if (pair && h->log2na >= 2 && (ipc % 4 == 0 || ipc >= 16)) {
+				pair = 2;
+				ipc = (ipc + 3) & ~3LL;
+			} else if (pair) {
+				ipc += ipc & 1;                                      // classes r, r+1 stay in one CTA
+			}
 			const int grid = (int)((items + ipc - 1) / ipc);
 			CU(ro::v2_launch(h->v2s, grid, s, h->d_scratch, NULL, h->d_tw_nb, d_rows + f0 * row_stride, row_stride,
 			                 items, 0, ipc, 0.f, h->log2na, pair, h->v2s.threads == 512 ? h->stagger : 0));
@@ -678,11 +685,22 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 			long long unit = h->v2s_grid_cap, a = unit, b = na;     // frames per wave = cap / gcd(cap, Na)
 			while (b) { long long t2 = a % b; a = b; b = t2; }
 			unit /= a;
-			long long budget_mb = 256;
+			// 512 MB: 64k frames 2.27 -> 2.40 M frames/s against 256 MB (B200, profiles/r02_scratch_mb_ab.txt)
+			long long budget_mb = 512;
 			if (cfg->scratch_mb > 0) budget_mb = cfg->scratch_mb;
 			const long long frame_bytes = 8LL * N;
 			long long units = (budget_mb << 20) / (unit * frame_bytes);
 			if (units < 1) units = 1;
+			// a CTA takes its items in pairs (Na = 2) or fours (Na >= 4), see the store stage of MODE_SPLIT: whole
+			// waves of pairs / fours keep every SM busy (13 items per CTA rounded up to 16 left 20 of 148 SMs idle)
+			if (!(cfg->tuning & RO_TUNE_NO_PAIR)) {
+				const long long grp = h->log2na >= 2 ? 4 : 2;
+				const long long ipu = std::max<long long>(1, unit * na / h->v2s_grid_cap);   // items per CTA and unit
+				long long g2 = grp, x = ipu % grp;
+				while (x) { long long t3 = g2 % x; g2 = x; x = t3; }                           // gcd(grp, ipu)
+				const long long step = grp / g2;
+				if (units > step) units -= units % step;
+			}
 			// the split kernel indexes frames with blockIdx.y: at most 65535 per launch
 			if (units * unit > 65535) units = std::max<long long>(1, 65535 / unit);
 			h->scratch_frames = std::min<long long>(units * unit, 65535);

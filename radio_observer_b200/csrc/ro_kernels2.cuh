@@ -59,7 +59,8 @@ struct Wf2Params {
 	int           log2na;       // MODE_SPLIT: the frame has Na = 2^log2na residue classes of N points each
 	int           stagger;      // serialise the shared-memory load bursts of the warps that share a scheduler
 	int           pair;         // MODE_SPLIT: rows are 16-byte aligned and every CTA starts on an even item:
-	                            // classes r, r+1 are stored together (see the store stage)
+	                            // classes r, r+1 are stored together (see the store stage); 2: every CTA starts on
+	                            // a multiple of four and classes 4j .. 4j+3 are stored together (Na >= 4)
 	// MODE_FUSED*: the first radix-Na step happens in this kernel (see the load stage)
 	const void   *raw;          // int16 I/Q of the whole batch
 	const float  *window_full;  // Na*N floats
@@ -182,6 +183,35 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned in
 	             :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// ---- tensor memory as a per-thread parking space -------------------------------------------------
+// The 256 KB of TMEM of an SM (512 columns x 128 lanes x 32 bit) are idle in these kernels: no tcgen05.mma
+// anywhere.  tcgen05.st / tcgen05.ld with shape 32x32b move N registers of every thread of a warp to / from N
+// consecutive columns of "its" lane (lane quarter = warp % 4), so a 512-thread CTA has 128 private words per
+// thread there -- room for the magnitudes of three residue classes (3 x 32 floats), which shared memory
+// (128 KB exchange buffer + 64 KB stash) cannot hold.
+__device__ __forceinline__ void tmem_st8(unsigned int taddr, const float (&v)[8])
+{
+	asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+	             :: "r"(taddr), "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])),
+	                "r"(__float_as_uint(v[3])), "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])),
+	                "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(unsigned int taddr, float (&v)[32])
+{
+	unsigned int r[32];
+	asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+	             "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+	             "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+	             : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+	               "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+	               "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+	               "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+	             : "r"(taddr) : "memory");
+	asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+	for (int i = 0; i < 32; i++) v[i] = __uint_as_float(r[i]);
+}
+
 // one raw I/Q pair -> packed complex float
 __device__ __forceinline__ c64 raw_to_c64(unsigned int w) { return short2_to_c64(w); }
 __device__ __forceinline__ c64 raw_to_c64(unsigned long long w) { return w; }
@@ -213,6 +243,12 @@ wf_fft2_kernel(const Wf2Params p)
 	constexpr bool F32 = MODE == MODE_DIRECT_F32;
 	constexpr int FLA = FUSED ? 1 : 0;   // log2(Na) of the fused modes
 	constexpr bool SPLIT = MODE == MODE_SPLIT || FUSED;
+	// MODE_SPLIT, 16k items, Na >= 4: the magnitudes of three residue classes wait in tensor memory for the
+	// fourth, see the store stage.  -DRO_SPLIT_TMEM=0 for the A/B.
+#ifndef RO_SPLIT_TMEM
+#define RO_SPLIT_TMEM 1
+#endif
+	constexpr bool SPLIT_TMEM = RO_SPLIT_TMEM && MODE == MODE_SPLIT && LOG2N == 14 && R3 == 16;
 #ifndef RO_FUSED_DIT
 #define RO_FUSED_DIT 1
 #endif
@@ -264,6 +300,20 @@ wf_fft2_kernel(const Wf2Params p)
 		mbar_init(bar_rd3, RO_WARP_ARRIVE ? T / 32 : T);
 	}
 	for (int i = t; i < WINF; i += T) win[i] = __ldg(p.window_half + i);
+	unsigned int tmem = 0;
+	if constexpr (SPLIT_TMEM) {
+		// all 512 columns: this kernel runs one CTA per SM (shared memory), nobody else on the SM wants any
+		unsigned int *slot = reinterpret_cast<unsigned int *>(mbar + 3);
+		if (t < 32) {
+			asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" :: "r"(smem_u32(slot)) : "memory");
+			asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+		}
+		asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+		__syncthreads();
+		asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+		// this thread's 128 columns: lane quarter of its warp, column block of its warp's level
+		tmem = *slot + ((unsigned int)(((t >> 5) & 3) * 32) << 16) + (unsigned int)((t >> 7) * 128);
+	}
 	__syncthreads();
 	if (STAGE && t == 0) {
 		mbar_expect_tx(mbar, 4u * N);
@@ -473,7 +523,10 @@ wf_fft2_kernel(const Wf2Params p)
 #pragma unroll
 			for (int n1 = 0; n1 < R1; n1++) v[n1] = __ldg(src + n1 * M + t);
 			ptxas_fence(p.stagger & 1);
-			// (prefetching the next item of the scratch into L2 here measured 12 % SLOWER: that path is HBM-bound)
+			// (prefetching the next item of the scratch into L2 here measured 12 % SLOWER, and bringing it into S
+			// with cp.async.bulk while the previous item is in pass 3 -- S is idle then, and thread t reads and writes
+			// the same column in pass 1 -- 10 % slower at 64k, 8 % at 128k: profiles/r02_split_tma_tmem_ab.txt.
+			// This path is bound by the bytes it moves through HBM, not by the latency of getting them.)
 		} else if (F32) {
 			// float32 pairs are packed complex already: straight into the transform's registers
 			const unsigned long long *src = reinterpret_cast<const unsigned long long *>(p.iq) + f * hop;
@@ -643,7 +696,57 @@ wf_fft2_kernel(const Wf2Params p)
 				const int r = (int)(f & ((1 << la) - 1));
 				float *row = p.rows + (f >> la) * p.row_stride;
 				const int big_mask = (N << la) - 1, big_half = (N << la) >> 1;
-				if (p.pair) {
+				if (SPLIT_TMEM && p.pair == 2 && la >= 2) {
+					// Na >= 4.  With pairs a thread wrote 8 bytes of every 4*Na: at Na = 4 half of a 32-byte sector
+					// now and the other half two items later, and every sector of the row made two partial trips
+					// to HBM (ncu, 64k: 243 KB read back and 121 KB written twice per 256 KB row).  Classes r = 4j ..
+					// 4j+2 now park their magnitudes in tensor memory (columns [k3/4][class][k3%4][c]) and class 4j+3
+					// stores all four: [c0 c1 c2 c3](k), 16 bytes, and at Na = 4 the thread's two outputs k = 2t,
+					// 2t+1 are one whole sector, which lane pairs exchange halves of so that every store
+					// instruction covers whole sectors.  The host hands every CTA a multiple of four items.
+					const int q = r & 3;
+					if (q != 3) {
+#pragma unroll
+						for (int g = 0; g < R3 / 4; g++) {
+							float pv[8];
+#pragma unroll
+							for (int i = 0; i < 4; i++) { pv[2 * i] = mag[4 * g + i][0]; pv[2 * i + 1] = mag[4 * g + i][1 % G]; }
+							tmem_st8(tmem + (unsigned int)(g * 32 + q * 8), pv);
+						}
+						asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+					} else {
+						const int odd = t & 1;
+#pragma unroll
+						for (int g = 0; g < R3 / 4; g++) {
+							float pv[32];
+							tmem_ld32(tmem + (unsigned int)(g * 32), pv);
+#pragma unroll
+							for (int i = 0; i < 4; i++) {
+								const int k3 = 4 * g + i;
+								const float4 a0 = make_float4(pv[2 * i], pv[8 + 2 * i], pv[16 + 2 * i], mag[k3][0]);
+								const float4 a1 = make_float4(pv[2 * i + 1], pv[8 + 2 * i + 1], pv[16 + 2 * i + 1], mag[k3][1 % G]);
+								const int k = k3 * (N / R3) + G * t;          // first of this thread's two outputs
+								if (la == 2) {
+									// sector of this thread: floats [8t, 8t + 8) of the k3 block = a0 | a1
+									const float4 snd = odd ? a0 : a1;
+									float4 rcv;
+									rcv.x = __shfl_xor_sync(0xffffffffu, snd.x, 1);
+									rcv.y = __shfl_xor_sync(0xffffffffu, snd.y, 1);
+									rcv.z = __shfl_xor_sync(0xffffffffu, snd.z, 1);
+									rcv.w = __shfl_xor_sync(0xffffffffu, snd.w, 1);
+									const int blk = (k3 * (N / R3)) << la;        // first bin of the k3 block
+									float *lo = row + ((blk + 8 * (t & ~1) + big_half) & big_mask) + 4 * odd;   // the even lane's sector
+									float *hi = row + ((blk + 8 * (t | 1) + big_half) & big_mask) + 4 * odd;    // the odd lane's sector
+									*reinterpret_cast<float4 *>(lo) = odd ? rcv : a0;
+									*reinterpret_cast<float4 *>(hi) = odd ? a1 : rcv;
+								} else {
+									*reinterpret_cast<float4 *>(row + (((k << la) + r - 3 + big_half) & big_mask)) = a0;
+									*reinterpret_cast<float4 *>(row + ((((k + 1) << la) + r - 3 + big_half) & big_mask)) = a1;
+								}
+							}
+						}
+					}
+				} else if (p.pair) {
 					// Alone, a class writes 4 bytes of every 4*Na: 32 scattered stores per thread and a
 					// queue of partial sectors (lg_throttle was the top stall).  Instead an even class
 					// parks its magnitudes in a thread-private slice of shared memory, and the odd class
@@ -734,6 +837,11 @@ wf_fft2_kernel(const Wf2Params p)
 				else row[off] = fast_sqrt(fmaf(zr, zr, zi * zi));
 			}
 		}
+	}
+	if constexpr (SPLIT_TMEM) {
+		asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+		__syncthreads();
+		if (t < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(*reinterpret_cast<unsigned int *>(mbar + 3)) : "memory");
 	}
 }
 

@@ -157,9 +157,15 @@ extern "C" int ro_wf_long_rows_static(int32_t device, int32_t bins, int32_t over
 	                        0, (long long)F, hop, (float)iq_gain));
 	const long long items = (long long)F << log2na;
 	long long ipc = (items + d->grid_cap - 1) / d->grid_cap;      // contiguous items per CTA
-	ipc += ipc & 1;                                               // classes r, r+1 stay in one CTA
+	int pair = 1;                                                 // classes r, r+1 stay in one CTA ...
+	if (log2na >= 2 && (ipc % 4 == 0 || ipc >= 16)) {             // ... or four of them (launch_fft, ro_cuda.cu)
+		pair = 2;
+		ipc = (ipc + 3) & ~3LL;
+	} else {
+		ipc += ipc & 1;
+	}
 	const int grid = (int)((items + ipc - 1) / ipc);
-	CUS(ro::v2_launch(d->k, grid, s, d->scratch, NULL, d_tw_nb, d_rows, bins, items, 0, ipc, 0.f, log2na, 1,
+	CUS(ro::v2_launch(d->k, grid, s, d->scratch, NULL, d_tw_nb, d_rows, bins, items, 0, ipc, 0.f, log2na, pair,
 	                  d->k.threads == 512 ? 14 : 0));
 	if (n_frames) *n_frames = F;
 	if (sync) CUS(cudaStreamSynchronize(s));

@@ -28,7 +28,8 @@ bool v2_pick_fused_f32(V2Kernel *out);
 // Launches it: n_frames items of `hop`-spaced N-sample windows of d_iq (int16 I/Q), or, for
 // V2_SPLIT, n_frames = frames*Na items of N packed complex floats each (d_iq = the scratch
 // written by v2_launch_split), whose outputs interleave into rows of Na*N floats; `pair` != 0
-// promises 16-byte aligned rows and an even frames_per_cta (classes r, r+1 are stored together).
+// promises 16-byte aligned rows and an even frames_per_cta (classes r, r+1 are stored together), `pair` == 2
+// a frames_per_cta that is a multiple of four (Na >= 4: classes 4j .. 4j+3 are stored together).
 cudaError_t v2_launch(const V2Kernel &k, int grid, cudaStream_t s, const void *d_iq, const float *d_window_half,
                       const float2 *d_tw, float *d_rows, long long row_stride, long long n_frames, long long hop,
                       long long frames_per_cta, float iq_gain, int log2na, int pair, int stagger);

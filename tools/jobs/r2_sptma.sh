@@ -1,0 +1,30 @@
+#!/bin/bash
+mkdir -p gpurun_out
+python -m pytest tests/test_gpu_parity.py tests/test_zz_no_alloc.py -x -q -m gpu 2>&1 | tail -3
+for rep in 1 2; do
+for v in base tma; do
+  if [ $v = base ]; then export RO_CUDA_LIB=$PWD/radio_observer_b200/csrc/_obj/libro_cuda_nosptma.so; else unset RO_CUDA_LIB; fi
+  for fmt in int16 float32; do
+  echo "## variant $v-$fmt rep $rep"
+  timeout 300 python tools/sweep.py --lo 16 --hi 18 --fmt $fmt | python -c "
+import sys, json
+for l in sys.stdin:
+    try: j = json.loads(l)
+    except Exception: continue
+    print(j.get('bins'), j.get('overlap'), round(j.get('Mframes_per_s', 0), 3), round(j.get('hbm_frac', 0), 4))
+"
+  done
+done
+done
+unset RO_CUDA_LIB
+for mb in 512 1024 2048; do
+echo "## variant tma-mb$mb rep 1"
+timeout 300 python tools/sweep.py --lo 16 --hi 17 --fmt int16 --scratch-mb $mb | python -c "
+import sys, json
+for l in sys.stdin:
+    try: j = json.loads(l)
+    except Exception: continue
+    print(j.get('bins'), j.get('overlap'), round(j.get('Mframes_per_s', 0), 3), round(j.get('hbm_frac', 0), 4))
+"
+done
+python tools/stress_determinism.py 2>&1 | tail -4
