@@ -196,6 +196,35 @@ __device__ __forceinline__ void tmem_st8(unsigned int taddr, const float (&v)[8]
 	                "r"(__float_as_uint(v[3])), "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])),
 	                "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])) : "memory");
 }
+// N packed complex values (2N words) of this thread to columns taddr .. taddr + 2N - 1
+__device__ __forceinline__ void tmem_st_c64(unsigned int taddr, const c64 (&v)[1])
+{
+	asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};"
+	             :: "r"(taddr), "r"((unsigned int)v[0]), "r"((unsigned int)(v[0] >> 32)) : "memory");
+}
+__device__ __forceinline__ void tmem_st_c64(unsigned int taddr, const c64 (&v)[2])
+{
+	asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};"
+	             :: "r"(taddr), "r"((unsigned int)v[0]), "r"((unsigned int)(v[0] >> 32)),
+	                "r"((unsigned int)v[1]), "r"((unsigned int)(v[1] >> 32)) : "memory");
+}
+// 16 packed complex values back from columns taddr .. taddr + 31 (no wait: tmem_wait_ld() before the first use)
+__device__ __forceinline__ void tmem_ld_c64x16(unsigned int taddr, c64 *v)
+{
+	unsigned int r[32];
+	asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+	             "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+	             "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+	             : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+	               "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+	               "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+	               "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+	             : "r"(taddr) : "memory");
+#pragma unroll
+	for (int i = 0; i < 16; i++) v[i] = (c64)r[2 * i] | ((c64)r[2 * i + 1] << 32);
+}
+__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_ld32(unsigned int taddr, float (&v)[32])
 {
 	unsigned int r[32];
@@ -249,6 +278,14 @@ wf_fft2_kernel(const Wf2Params p)
 #define RO_SPLIT_TMEM 1
 #endif
 	constexpr bool SPLIT_TMEM = RO_SPLIT_TMEM && MODE == MODE_SPLIT && LOG2N == 14 && R3 == 16;
+	// MODE_FUSED1*: the odd class y_1 of a frame (32 packed complex per thread) waits in tensor memory for its turn
+	// instead of in a CTA-private slice of global memory (128 KB out to L2 and 128 KB back per frame, of the 576 KB
+	// a frame moved in all).  -DRO_FUSED_TMEM=0 for the A/B.
+#ifndef RO_FUSED_TMEM
+#define RO_FUSED_TMEM 1
+#endif
+	constexpr bool FUSED_TMEM = RO_FUSED_TMEM && FUSED && LOG2N == 14 && R3 == 16;
+	constexpr bool USE_TMEM = SPLIT_TMEM || FUSED_TMEM;
 #ifndef RO_FUSED_DIT
 #define RO_FUSED_DIT 1
 #endif
@@ -301,7 +338,7 @@ wf_fft2_kernel(const Wf2Params p)
 	}
 	for (int i = t; i < WINF; i += T) win[i] = __ldg(p.window_half + i);
 	unsigned int tmem = 0;
-	if constexpr (SPLIT_TMEM) {
+	if constexpr (USE_TMEM) {
 		// all 512 columns: this kernel runs one CTA per SM (shared memory), nobody else on the SM wants any
 		unsigned int *slot = reinterpret_cast<unsigned int *>(mbar + 3);
 		if (t < 32) {
@@ -485,6 +522,7 @@ wf_fft2_kernel(const Wf2Params p)
 						}
 					}
 					ptxas_fence(p.stagger & 1);
+					c64 y1[2][HP];                     // the odd class at the low and the high positions of this burst
 #pragma unroll
 					for (int jj = 0; jj < 2 * HP; jj++) {
 						const int n1 = jj < HP ? b * HP + jj : R1 - (b + 1) * HP + (jj - HP);
@@ -496,7 +534,13 @@ wf_fft2_kernel(const Wf2Params p)
 						fft_dif2<2>(xq);
 						xq[1] = cmul2(cmul2(xq[1], wt1), cw64(n1), -sw64(n1));
 						v[n1] = xq[0];
-						scr[m] = xq[1];
+						if (FUSED_TMEM) y1[jj / HP][jj % HP] = xq[1];
+						else scr[m] = xq[1];
+					}
+					if constexpr (FUSED_TMEM) {
+						// columns 2*n1, 2*n1 + 1 of this thread's 128
+						tmem_st_c64(tmem + (unsigned int)(2 * b * HP), y1[0]);
+						tmem_st_c64(tmem + (unsigned int)(2 * (R1 - (b + 1) * HP)), y1[1]);
 					}
 					// the values are in registers and used: the stage may be refilled
 					__syncwarp();
@@ -509,6 +553,11 @@ wf_fft2_kernel(const Wf2Params p)
 						asm volatile("prefetch.global.L2 [%0];" :: "l"(nx + o));
 				}
 #endif
+			} else if (FUSED_TMEM) {
+				tmem_wait_st();
+				tmem_ld_c64x16(tmem, &v[0]);
+				tmem_ld_c64x16(tmem + 32u, &v[16]);
+				tmem_wait_ld();
 			} else {
 				const unsigned long long *src = scr + (r - 1) * N;
 				ptxas_fence(p.stagger & 1);
@@ -838,7 +887,7 @@ wf_fft2_kernel(const Wf2Params p)
 			}
 		}
 	}
-	if constexpr (SPLIT_TMEM) {
+	if constexpr (USE_TMEM) {
 		asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 		__syncthreads();
 		if (t < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(*reinterpret_cast<unsigned int *>(mbar + 3)) : "memory");
