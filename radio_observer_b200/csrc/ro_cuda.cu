@@ -616,6 +616,7 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 				CUH(cudaFuncSetAttribute(h->v2[st].fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->v2[st].smem));
 				int occ2 = 0;
 				CUH(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, h->v2[st].fn, h->v2[st].threads, h->v2[st].smem));
+				if (ro::v2_tmem_cols(h->v2[st]) > 0) occ2 = std::min(occ2, 512 / ro::v2_tmem_cols(h->v2[st]));   // tensor-memory columns per SM
 				if (occ2 < 1) { h->v2_ok = false; break; }
 				h->v2_grid_cap[st] = occ2 * h->n_sms;
 			}
@@ -628,6 +629,7 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 			CUH(cudaFuncSetAttribute(h->v2[0].fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->v2[0].smem));
 			int occ2 = 0;
 			CUH(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, h->v2[0].fn, h->v2[0].threads, h->v2[0].smem));
+			if (ro::v2_tmem_cols(h->v2[0]) > 0) occ2 = std::min(occ2, 512 / ro::v2_tmem_cols(h->v2[0]));   // tensor-memory columns per SM
 			if (occ2 >= 1) {
 				h->v2_grid_cap[0] = h->v2_grid_cap[1] = occ2 * h->n_sms;
 				h->v2_ok = h->v2_f32 = true;
@@ -671,6 +673,7 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 		CUH(cudaFuncSetAttribute(h->v2s.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->v2s.smem));
 		int occ3 = 0;
 		CUH(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ3, h->v2s.fn, h->v2s.threads, h->v2s.smem));
+		if (ro::v2_tmem_cols(h->v2s) > 0) occ3 = std::min(occ3, 512 / ro::v2_tmem_cols(h->v2s));   // tensor-memory columns per SM
 		if (occ3 >= 1) {
 			h->v2s_grid_cap = occ3 * h->n_sms;
 			std::vector<float> twb(2 * (size_t)NBv);
@@ -714,6 +717,7 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 		CUH(cudaFuncSetAttribute(h->v2f.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->v2f.smem));
 		int occ4 = 0;
 		CUH(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, h->v2f.fn, h->v2f.threads, h->v2f.smem));
+		if (ro::v2_tmem_cols(h->v2f) > 0) occ4 = std::min(occ4, 512 / ro::v2_tmem_cols(h->v2f));   // tensor-memory columns per SM
 		if (occ4 >= 1) {
 			h->v2f_grid_cap = occ4 * h->n_sms;
 			const size_t per_cta = (((size_t)1 << h->log2na) - 1) * ((size_t)1 << 14) * sizeof(float2);

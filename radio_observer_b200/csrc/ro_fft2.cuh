@@ -173,6 +173,40 @@ __device__ __forceinline__ void twiddle_powers2(c64 (&v)[R], const c64 (&base)[i
 	}
 }
 
+// The R factors twiddle_powers2 multiplies by, w[k] = base-composed w^k (w[0] = 1), with exactly its composition
+// (same products in the same order, so a kernel that keeps them and multiplies later gives the same bits).
+template <int R>
+__device__ __forceinline__ void twiddle_table2(c64 (&w)[R], const c64 (&base)[ilog2(R)])
+{
+	constexpr int L = ilog2(R);
+	constexpr int LB = (L + 1) / 2;
+	constexpr int NLO = 1 << LB;
+	constexpr int NHI = 1 << (L - LB);
+	c64 lo[NLO];
+	lo[0] = pk(1.f, 0.f);
+#pragma unroll
+	for (int msb = 0; msb < LB; msb++) {
+		lo[1 << msb] = base[msb];
+#pragma unroll
+		for (int rest = 1; rest < (1 << msb); rest++)
+			lo[(1 << msb) + rest] = cmul2(lo[rest], base[msb]);
+	}
+	c64 hi[NHI];
+	hi[0] = pk(1.f, 0.f);
+#pragma unroll
+	for (int msb = 0; msb < L - LB; msb++) {
+		hi[1 << msb] = base[LB + msb];
+#pragma unroll
+		for (int rest = 1; rest < (1 << msb); rest++)
+			hi[(1 << msb) + rest] = cmul2(hi[rest], base[LB + msb]);
+	}
+#pragma unroll
+	for (int h = 0; h < NHI; h++)
+#pragma unroll
+		for (int j = 0; j < NLO; j++)
+			w[h * NLO + j] = h == 0 ? lo[j] : (j == 0 ? hi[h] : cmul2(lo[j], hi[h]));
+}
+
 // ---- int16 I/Q -> packed float without the XU pipe --------------------------
 // cvt.rn.f32.s16 runs on the 16-lane XU pipe (measured 0.5 warp-instr/clk/SM).
 // Instead: flip the sign bits (x + 32768 as unsigned), splice the 16 bits into

@@ -223,6 +223,30 @@ __device__ __forceinline__ void tmem_ld_c64x16(unsigned int taddr, c64 *v)
 #pragma unroll
 	for (int i = 0; i < 16; i++) v[i] = (c64)r[2 * i] | ((c64)r[2 * i + 1] << 32);
 }
+// 8 packed complex values to / from columns taddr .. taddr + 15
+__device__ __forceinline__ void tmem_st_c64x8(unsigned int taddr, const c64 *v)
+{
+	asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+	             "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+	             :: "r"(taddr),
+	                "r"((unsigned int)v[0]), "r"((unsigned int)(v[0] >> 32)), "r"((unsigned int)v[1]), "r"((unsigned int)(v[1] >> 32)),
+	                "r"((unsigned int)v[2]), "r"((unsigned int)(v[2] >> 32)), "r"((unsigned int)v[3]), "r"((unsigned int)(v[3] >> 32)),
+	                "r"((unsigned int)v[4]), "r"((unsigned int)(v[4] >> 32)), "r"((unsigned int)v[5]), "r"((unsigned int)(v[5] >> 32)),
+	                "r"((unsigned int)v[6]), "r"((unsigned int)(v[6] >> 32)), "r"((unsigned int)v[7]), "r"((unsigned int)(v[7] >> 32))
+	             : "memory");
+}
+__device__ __forceinline__ void tmem_ld_c64x8(unsigned int taddr, c64 (&v)[8])
+{
+	unsigned int r[16];
+	asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+	             "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+	             : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+	               "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+	             : "r"(taddr) : "memory");
+	asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+	for (int i = 0; i < 8; i++) v[i] = (c64)r[2 * i] | ((c64)r[2 * i + 1] << 32);
+}
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_ld32(unsigned int taddr, float (&v)[32])
@@ -244,6 +268,19 @@ __device__ __forceinline__ void tmem_ld32(unsigned int taddr, float (&v)[32])
 // one raw I/Q pair -> packed complex float
 __device__ __forceinline__ c64 raw_to_c64(unsigned int w) { return short2_to_c64(w); }
 __device__ __forceinline__ c64 raw_to_c64(unsigned long long w) { return w; }
+
+// columns of tensor memory a CTA of the kernel allocates (0: none); see TW_TMEM / SPLIT_TMEM / FUSED_TMEM in the kernel
+__host__ __device__ constexpr int wf2_tmem_cols_of(int log2n, int threads, bool split_mode)
+{
+	// every user is a 16k kernel: 512 threads, one CTA per SM, all 512 columns, 128 per thread
+	(void)split_mode;
+	return (log2n == 14 && threads == 512) ? 512 : 0;
+}
+template <int LOG2N, int P, int MODE>
+__host__ __device__ constexpr int wf2_tmem_cols()
+{
+	return wf2_tmem_cols_of(LOG2N, (1 << LOG2N) / P, mode_is_split(MODE));
+}
 
 // bytes of dynamic shared memory the kernel needs
 template <int LOG2N, int P, int R3, int MODE>
@@ -285,7 +322,23 @@ wf_fft2_kernel(const Wf2Params p)
 #define RO_FUSED_TMEM 1
 #endif
 	constexpr bool FUSED_TMEM = RO_FUSED_TMEM && FUSED && LOG2N == 14 && R3 == 16;
-	constexpr bool USE_TMEM = SPLIT_TMEM || FUSED_TMEM;
+	// One-kernel modes, 16k: the 31 + 31 twiddle factors a thread multiplies its pass-1 and pass-2 outputs by are
+	// the same for every frame (W_N^(t*k1), W_512^(n3*k2)).  They used to be rebuilt from five table entries each
+	// in every frame (26 complex multiplications per pass before the 31 that apply them: 104 of the 824 packed
+	// instructions of a frame); now they are composed once, the same way, parked in the thread's 124 words of
+	// tensor memory and read back eight at a time.  -DRO_TW_TMEM=0 for the A/B.
+#ifndef RO_TW_TMEM
+#define RO_TW_TMEM 1
+#endif
+	// 16k only.  The same for the smaller kernels (4*P words per thread, 4*P*T/128 columns per CTA: 256 at 8k,
+	// 128 at 4k, 64 at 2k) measured SLOWER on B200: 8k +0.5 % (int16) / -8 % (float32), 4k -13 %, 2k -40 %
+	// (profiles/r02_tw_tmem_ab.txt): their transforms are too short to cover the tcgen05.ld round trips.
+	// The host never asks for more resident CTAs than 512 columns allow (v2_tmem_cols, ro_cuda.cu).
+	constexpr bool TW_TMEM = RO_TW_TMEM && !SPLIT && wf2_tmem_cols<LOG2N, P, MODE>() > 0;
+	constexpr bool USE_TMEM = SPLIT_TMEM || FUSED_TMEM || TW_TMEM;
+	constexpr int TMEM_COLS = wf2_tmem_cols<LOG2N, P, MODE>();
+	constexpr int TMEM_T = (1 << LOG2N) / P;                                                   // threads of the CTA
+	constexpr int TMEM_PER_LEVEL = (TMEM_T >= 128) ? TMEM_COLS / (TMEM_T / 128) : TMEM_COLS;  // columns of one thread
 #ifndef RO_FUSED_DIT
 #define RO_FUSED_DIT 1
 #endif
@@ -339,17 +392,17 @@ wf_fft2_kernel(const Wf2Params p)
 	for (int i = t; i < WINF; i += T) win[i] = __ldg(p.window_half + i);
 	unsigned int tmem = 0;
 	if constexpr (USE_TMEM) {
-		// all 512 columns: this kernel runs one CTA per SM (shared memory), nobody else on the SM wants any
+		// the long-frame modes take all 512 columns: one CTA per SM (shared memory), nobody else on the SM wants any
 		unsigned int *slot = reinterpret_cast<unsigned int *>(mbar + 3);
 		if (t < 32) {
-			asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" :: "r"(smem_u32(slot)) : "memory");
+			asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(slot)), "n"(TMEM_COLS) : "memory");
 			asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
 		}
 		asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 		__syncthreads();
 		asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 		// this thread's 128 columns: lane quarter of its warp, column block of its warp's level
-		tmem = *slot + ((unsigned int)(((t >> 5) & 3) * 32) << 16) + (unsigned int)((t >> 7) * 128);
+		tmem = *slot + ((unsigned int)(((t >> 5) & 3) * 32) << 16) + (unsigned int)((t >> 7) * TMEM_PER_LEVEL);
 	}
 	__syncthreads();
 	if (STAGE && t == 0) {
@@ -373,6 +426,33 @@ wf_fft2_kernel(const Wf2Params p)
 		}
 	}
 	const c64 gain2 = pk(0.f, p.iq_gain);
+	if constexpr (TW_TMEM) {
+		c64 w[P];
+		twiddle_table2<R1>(w, b1);
+#pragma unroll
+		for (int c = 0; c < P / 8; c++) tmem_st_c64x8(tmem + (unsigned int)(16 * c), &w[8 * c]);
+		twiddle_table2<R2>(w, b2);
+#pragma unroll
+		for (int c = 0; c < P / 8; c++) tmem_st_c64x8(tmem + (unsigned int)(2 * P + 16 * c), &w[8 * c]);
+		tmem_wait_st();
+	}
+	// v[bitrev(k)] *= (parked factor k), k = 1 .. P-1; col0: first column of the pass's table
+	auto twiddle_tmem = [&](c64 (&v)[P], unsigned int col0) {
+		if constexpr (TW_TMEM) {
+#pragma unroll
+			for (int c = 0; c < P / 8; c++) {
+				c64 w[8];
+				tmem_ld_c64x8(tmem + col0 + (unsigned int)(16 * c), w);
+#pragma unroll
+				for (int j = 0; j < 8; j++) {
+					const int k = 8 * c + j;
+					if (k == 0) continue;
+					v[bitrev(k, LP)] = cmul2(v[bitrev(k, LP)], w[j]);
+				}
+			}
+		}
+	};
+	static_assert(!TW_TMEM || 4 * P <= TMEM_PER_LEVEL, "tensor-memory columns per thread");
 
 	// ---- MODE_FUSED1*: the load phase of a 2N-point frame, staged by TMA ----
 	// A frame of 2N points needs, for every position m = n1*M + t of this thread, the samples and window
@@ -626,7 +706,8 @@ wf_fft2_kernel(const Wf2Params p)
 		RO_TP(2);
 		fft_fwd2<R1, USE_DIT>(v);
 		RO_SITE(0, p.stagger & 1);
-		twiddle_powers2<R1>(v, b1);
+		if (TW_TMEM) twiddle_tmem(v, 0u);
+		else twiddle_powers2<R1>(v, b1);
 		RO_SITE(1, p.stagger & 1);
 		RO_TP(3);
 		// S still holds the previous frame's pass-3 inputs until every thread has read them
@@ -681,7 +762,8 @@ wf_fft2_kernel(const Wf2Params p)
 			RO_TP(8);
 			fft_fwd2<R2, USE_DIT>(v);
 			RO_SITE(2, p.stagger & 1);
-			twiddle_powers2<R2>(v, b2);
+			if (TW_TMEM) twiddle_tmem(v, 2u * P);
+			else twiddle_powers2<R2>(v, b2);
 			RO_SITE(3, p.stagger & 1);
 			RO_TP(9);
 			mbar_wait(bar_rd2, (unsigned int)(f - f0) & 1u);   // ... and so are everyone else's
@@ -890,7 +972,7 @@ wf_fft2_kernel(const Wf2Params p)
 	if constexpr (USE_TMEM) {
 		asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 		__syncthreads();
-		if (t < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(*reinterpret_cast<unsigned int *>(mbar + 3)) : "memory");
+		if (t < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(*reinterpret_cast<unsigned int *>(mbar + 3)), "n"(TMEM_COLS) : "memory");
 	}
 }
 

@@ -84,6 +84,11 @@ bool v2_pick(int log2n, int mode, bool gain, V2Kernel *out)
 	}
 }
 
+int v2_tmem_cols(const V2Kernel &k)
+{
+	return wf2_tmem_cols_of(k.log2n, k.threads, k.mode == V2_SPLIT || k.mode == V2_FUSED1 || k.mode == V2_FUSED1_F32);
+}
+
 cudaError_t v2_launch(const V2Kernel &k, int grid, cudaStream_t s, const void *d_iq, const float *d_window_half,
                       const float2 *d_tw, float *d_rows, long long row_stride, long long n_frames, long long hop,
                       long long frames_per_cta, float iq_gain, int log2na, int pair, int stagger)

@@ -25,6 +25,10 @@ bool v2_pick_f32(int log2n, bool gain, V2Kernel *out);
 // V2_FUSED1 for float32 I/Q (frames of 2*16384 points), launched with v2_launch_fused.
 bool v2_pick_fused_f32(V2Kernel *out);
 
+// Columns of tensor memory one CTA of the kernel allocates for its whole life (0: none): at most 512 / this many
+// CTAs may be resident on an SM, a CTA beyond that waits in tcgen05.alloc until another one exits.
+int v2_tmem_cols(const V2Kernel &k);
+
 // Launches it: n_frames items of `hop`-spaced N-sample windows of d_iq (int16 I/Q), or, for
 // V2_SPLIT, n_frames = frames*Na items of N packed complex floats each (d_iq = the scratch
 // written by v2_launch_split), whose outputs interleave into rows of Na*N floats; `pair` != 0
