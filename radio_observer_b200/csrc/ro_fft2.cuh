@@ -211,6 +211,8 @@ __device__ __forceinline__ void twiddle_table2(c64 (&w)[R], const c64 (&base)[il
 // cvt.rn.f32.s16 runs on the 16-lane XU pipe (measured 0.5 warp-instr/clk/SM).
 // Instead: flip the sign bits (x + 32768 as unsigned), splice the 16 bits into
 // the mantissa of 2^23 with PRMT, subtract 2^23 + 32768: exact, ALU + FMA pipes.
+// (Round 2 tried the XU pipe again now that the kernels sit on the FMA pipe -- two I2F.S16, the second with the
+// .H1 selector, no other instruction: 1k -5 %, 8k -7 %, 16k -1.4 %, the rest +-0.5 %, profiles/r02_cvt_xu_ab.txt.)
 __device__ __forceinline__ c64 short2_to_c64(unsigned int v)
 {
 	const unsigned int u = v ^ 0x80008000u;

@@ -156,6 +156,42 @@ def test_fused_long_frames_many_frames_per_cta(bins, fmt, overlap, iq_gain):
     assert_rows_close(rows, ref, f"{fmt} fused N={bins} ov={overlap}")
 
 
+@pytest.mark.parametrize("bins,hop,fmt,iq_gain", [
+    (65536, 52, "int16", 0.0), (65536, 40, "float32", -1.5), (131072, 36, "int16", 4.0), (262144, 20, "int16", 0.0),
+])
+def test_long_frames_four_classes_stored_together(bins, hop, fmt, iq_gain):
+    """Na >= 4 (64k and up): with at least 16 items per CTA the split path parks the magnitudes of three
+    residue classes in tensor memory (tcgen05.st / tcgen05.ld) and the fourth class stores 16-byte quads
+    -- whole 32-byte sectors at 64k, lane pairs exchanging halves.  One device-resident call with enough
+    frames for that on any SM count up to 160 (the host-buffer path cuts a call into chunks too short for
+    it, and the short cases above run the pair stores), every CTA walking several groups of four, so the
+    parked columns are reused; against the oracle, row for row."""
+    na = bins // 16384
+    n_frames = 16 * 160 // na + 3
+    n = bins + (n_frames - 1) * hop + 1
+    spec = synth.SynthSpec(sample_rate=96000, n_samples=n, seed=bins // 1024 + hop, carrier_freq=21999.7)
+    if fmt == "int16":
+        iq, in_format = synth.generate_int16(spec), ro.IN_INT16
+    else:
+        iq, in_format = synth.generate_float32(spec), ro.IN_FLOAT32
+    wf = ro.Waterfall(bins, bins - hop, sample_rate=96000, in_format=in_format, iq_gain=iq_gain)
+    d_in, d_rows = DeviceBuffer(iq.nbytes), DeviceBuffer(4 * bins * n_frames)
+    try:
+        d_in.upload(iq)
+        ro.load_library().ro_dev_memset(0, d_rows.ptr, 0xFF, d_rows.nbytes)
+        assert wf.process_resident(d_in.ptr, n, d_rows.ptr, None) == n_frames
+        assert "MODE_SPLIT" in wf.kernel_name()
+        rows = d_rows.download(np.float32, n_frames * bins).reshape(n_frames, bins)
+    finally:
+        wf.close()
+        d_in.free()
+        d_rows.free()
+    ref = R.waterfall_rows(iq, bins, bins - hop, iq_gain=iq_gain)
+    assert len(ref) == n_frames
+    assert np.isfinite(rows).all()
+    assert_rows_close(rows, ref, f"{fmt} quads N={bins} hop={hop}")
+
+
 def test_complex64_input_is_narrowed_like_float32():
     bins, overlap = 4096, 3072
     spec = synth.SynthSpec(sample_rate=48000, n_samples=bins * 4, seed=3)
