@@ -247,6 +247,23 @@ __device__ __forceinline__ void tmem_ld_c64x8(unsigned int taddr, c64 (&v)[8])
 #pragma unroll
 	for (int i = 0; i < 8; i++) v[i] = (c64)r[2 * i] | ((c64)r[2 * i + 1] << 32);
 }
+// N floats from columns taddr .. taddr + N - 1 (N = 2, 4; no wait)
+__device__ __forceinline__ void tmem_ld_f(unsigned int taddr, float (&v)[2])
+{
+	unsigned int a, b;
+	asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "r"(taddr) : "memory");
+	v[0] = __uint_as_float(a); v[1] = __uint_as_float(b);
+}
+__device__ __forceinline__ void tmem_ld_f(unsigned int taddr, float (&v)[4])
+{
+	unsigned int a, b, c, d;
+	asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(taddr) : "memory");
+	v[0] = __uint_as_float(a); v[1] = __uint_as_float(b); v[2] = __uint_as_float(c); v[3] = __uint_as_float(d);
+}
+__device__ __forceinline__ void tmem_st_f(unsigned int taddr, const float (&v)[8])
+{
+	tmem_st8(taddr, v);
+}
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_ld32(unsigned int taddr, float (&v)[32])
@@ -322,6 +339,12 @@ wf_fft2_kernel(const Wf2Params p)
 #define RO_FUSED_TMEM 1
 #endif
 	constexpr bool FUSED_TMEM = RO_FUSED_TMEM && FUSED && LOG2N == 14 && R3 == 16;
+	// ... and next to it (columns 64 .. 127) the 2 x 32 window values the thread ever uses, which used to travel with
+	// every TMA burst.  -DRO_FUSED_WIN_TMEM=0: they do again (A/B).
+#ifndef RO_FUSED_WIN_TMEM
+#define RO_FUSED_WIN_TMEM 1
+#endif
+	constexpr bool WIN_TMEM = RO_FUSED_WIN_TMEM && FUSED_TMEM;
 	// One-kernel modes, 16k: the 31 + 31 twiddle factors a thread multiplies its pass-1 and pass-2 outputs by are
 	// the same for every frame (W_N^(t*k1), W_512^(n3*k2)).  They used to be rebuilt from five table entries each
 	// in every frame (26 complex multiplications per pass before the 31 that apply them: 104 of the 824 packed
@@ -436,6 +459,21 @@ wf_fft2_kernel(const Wf2Params p)
 		for (int c = 0; c < P / 8; c++) tmem_st_c64x8(tmem + (unsigned int)(2 * P + 16 * c), &w[8 * c]);
 		tmem_wait_st();
 	}
+	if constexpr (WIN_TMEM) {
+		// the 2 x 32 window values this thread ever uses, w[q*N + n1*M + t], to columns 64 + 2*n1 + q: they used to
+		// travel with every burst (two of the six copies, a third of its bytes)
+#pragma unroll
+		for (int c = 0; c < R1 / 4; c++) {
+			float wq[8];
+#pragma unroll
+			for (int i = 0; i < 4; i++) {
+				wq[2 * i] = __ldg(p.window_full + (4 * c + i) * M + t);
+				wq[2 * i + 1] = __ldg(p.window_full + N + (4 * c + i) * M + t);
+			}
+			tmem_st_f(tmem + 64u + (unsigned int)(8 * c), wq);
+		}
+		tmem_wait_st();
+	}
 	// v[bitrev(k)] *= (parked factor k), k = 1 .. P-1; col0: first column of the pass's table
 	auto twiddle_tmem = [&](c64 (&v)[P], unsigned int col0) {
 		if constexpr (TW_TMEM) {
@@ -480,7 +518,9 @@ wf_fft2_kernel(const Wf2Params p)
 	constexpr int RAWB = FIN32 ? 8 : 4;
 	constexpr int HP = FIN32 ? 1 : 2;                              // positions per burst from each end
 	constexpr unsigned int RUN_RAW = (unsigned int)(HP * M) * RAWB, RUN_WIN = (unsigned int)(HP * M) * 4u;
-	constexpr unsigned int SB = 4u * RUN_RAW + 2u * RUN_WIN;       // bytes per stage: 24 KB (int16), 20 KB (float32)
+	// bytes per stage: four sample runs, and unless the window waits in tensor memory two window runs:
+	// 16 KB (24 KB with window) for int16, 16 KB (20 KB) for float32
+	constexpr unsigned int SB = 4u * RUN_RAW + (WIN_TMEM ? 0u : 2u * RUN_WIN);
 	constexpr int NST = 3;
 	constexpr int NB = R1 / (2 * HP);                              // bursts per frame
 	static_assert(!FUSED || (SB <= FUSED_RING_BYTES && 2 * SB <= 4u * N), "ring");
@@ -498,7 +538,7 @@ wf_fft2_kernel(const Wf2Params p)
 			mbar_wait(emptyb + s, ((fullph >> s) & 1u) ^ 1u);
 			if (lane == 0) mbar_expect_tx(fullb + s, SB);
 			__syncwarp();
-			if (lane < 6) {
+			if (lane < (WIN_TMEM ? 4 : 6)) {
 				const int pos0 = (lane & 1) ? R1 - (b + 1) * HP : b * HP;      // odd lanes: the high end
 				unsigned char *dst = stage_ptr(s);
 				if (lane < 4)      // sample run q = lane / 2
@@ -588,6 +628,11 @@ wf_fft2_kernel(const Wf2Params p)
 						const unsigned char *st = stage_ptr(s);
 						const raw_t *rr = reinterpret_cast<const raw_t *>(st);
 						const float *wl = reinterpret_cast<const float *>(st + 4 * RUN_RAW), *wh = wl + HP * M;
+						float wlo[2 * HP], whi[2 * HP];         // WIN_TMEM: [position][q] of the low and the high run
+						if constexpr (WIN_TMEM) {
+							tmem_ld_f(tmem + 64u + (unsigned int)(2 * b * HP), wlo);
+							tmem_ld_f(tmem + 64u + (unsigned int)(2 * (R1 - (b + 1) * HP)), whi);
+						}
 #pragma unroll
 						for (int j = 0; j < HP; j++) {
 							// j: low position b*HP + j;  HP + j: high position R1 - (b+1)*HP + j
@@ -595,10 +640,20 @@ wf_fft2_kernel(const Wf2Params p)
 							raw[HP + j][0] = rr[1 * HP * M + j * M + t];
 							raw[j][1] = rr[2 * HP * M + j * M + t];
 							raw[HP + j][1] = rr[3 * HP * M + j * M + t];
-							wv[j][0] = wl[j * M + t];
-							wv[HP + j][0] = wh[j * M + t];
-							wv[j][1] = wh[(HP - 1 - j) * M + (M - 1 - t)];
-							wv[HP + j][1] = wl[(HP - 1 - j) * M + (M - 1 - t)];
+							if constexpr (!WIN_TMEM) {
+								wv[j][0] = wl[j * M + t];
+								wv[HP + j][0] = wh[j * M + t];
+								wv[j][1] = wh[(HP - 1 - j) * M + (M - 1 - t)];
+								wv[HP + j][1] = wl[(HP - 1 - j) * M + (M - 1 - t)];
+							}
+						}
+						if constexpr (WIN_TMEM) {
+							tmem_wait_ld();
+#pragma unroll
+							for (int j = 0; j < HP; j++) {
+								wv[j][0] = wlo[2 * j]; wv[j][1] = wlo[2 * j + 1];
+								wv[HP + j][0] = whi[2 * j]; wv[HP + j][1] = whi[2 * j + 1];
+							}
 						}
 					}
 					ptxas_fence(p.stagger & 1);
