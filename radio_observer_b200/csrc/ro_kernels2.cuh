@@ -505,14 +505,16 @@ wf_fft2_kernel(const Wf2Params p)
 	// sample runs (q = 0, 1 x low, high) and two window runs (low, high), six cp.async.bulk copies that
 	// complete on the stage's `full` mbarrier.  Every warp reads its 32 columns with LDS (the q = 1 window
 	// value of a low position is element M-1-t of the mirrored segment in the high run, and vice versa)
-	// and releases the stage on its `empty` mbarrier (one arrival per warp).  The ring has three stages:
-	// stage 0 is memory of its own, stages 1 and 2 live in the 64 KB magnitude stash, which is idle
-	// during the load phase (written in pass 3 of the even class, read in pass 3 of the odd class; the
-	// last readers of a frame arrive on `stashfree`).  Burst b uses stage b % 3.  Schedule, no shared
-	// producer state: burst 0 of the next frame is issued right after this frame's load phase (a whole
-	// frame ahead), bursts 1 and 2 at the start of the load phase, burst b + 2 when warp b % 16 starts
-	// burst b; the empty-barrier parity to wait for is the complement of the consumer's own phase bit of
-	// that stage (its last use has been consumed).
+	// and releases the stage on its `empty` mbarrier (one arrival per warp).  The ring has ND stages of
+	// memory of their own and NS that live in the 64 KB magnitude stash, which is idle during the load
+	// phase (written in pass 3 of the even class, read in pass 3 of the odd class; the last readers of a
+	// frame arrive on `stashfree`): 1 + 2 stages of 24 KB while the window runs travelled with the bursts,
+	// 2 + 4 of 16 KB since the window waits in tensor memory (WIN_TMEM).  Burst b uses stage b % NST.
+	// Schedule, no shared producer state: bursts 0 .. ND-1 of the next frame are issued right after this
+	// frame's load phase (a whole frame ahead), bursts ND .. NST-1 at the start of the load phase, burst
+	// b + NST - 1 when warp b % 16 starts burst b (into the stage burst b - 1 has just left); the
+	// empty-barrier parity to wait for is the complement of the consumer's own phase bit of that stage
+	// (its last use has been consumed).
 	static_assert(!FUSED || FLA == 1, "the fused kernel does the radix-2 step only");
 	constexpr int FNA = 1 << FLA;
 	constexpr int RAWB = FIN32 ? 8 : 4;
@@ -521,7 +523,14 @@ wf_fft2_kernel(const Wf2Params p)
 	// bytes per stage: four sample runs, and unless the window waits in tensor memory two window runs:
 	// 16 KB (24 KB with window) for int16, 16 KB (20 KB) for float32
 	constexpr unsigned int SB = 4u * RUN_RAW + (WIN_TMEM ? 0u : 2u * RUN_WIN);
-	constexpr int NST = 3;
+	// ring: ND stages of memory of their own (filled a whole frame ahead), NS more in the magnitude stash (filled at
+	// the start of the load phase); 1 + 2 with the window runs in the bursts, 2 + 4 without.  -DRO_FUSED_RING3=1: 1 + 2.
+#ifndef RO_FUSED_RING3
+#define RO_FUSED_RING3 0
+#endif
+	constexpr int ND = RO_FUSED_RING3 ? 1 : (int)(FUSED_RING_BYTES / SB), NS = RO_FUSED_RING3 ? 2 : (int)(4u * N / SB);
+	constexpr int NST = ND + NS;
+	static_assert(!FUSED || (NST >= 3 && NST <= 8 && (2 * NST + 1) * 8 <= (int)FUSED_BAR_BYTES), "ring stages");
 	constexpr int NB = R1 / (2 * HP);                              // bursts per frame
 	static_assert(!FUSED || (SB <= FUSED_RING_BYTES && 2 * SB <= 4u * N), "ring");
 	unsigned char *stash8 = reinterpret_cast<unsigned char *>(mbar + 4);
@@ -529,12 +538,12 @@ wf_fft2_kernel(const Wf2Params p)
 	unsigned long long *fullb = reinterpret_cast<unsigned long long *>(ded8 + FUSED_RING_BYTES);
 	unsigned long long *emptyb = fullb + NST, *stashfree = emptyb + NST;
 	unsigned int fullph = 0, stashph = 1;       // a fresh barrier passes a wait on parity 1
-	auto stage_ptr = [&](int s) -> unsigned char * { return s == 0 ? ded8 : stash8 + (s - 1) * SB; };
+	auto stage_ptr = [&](int s) -> unsigned char * { return s < ND ? ded8 + s * SB : stash8 + (s - ND) * SB; };
 	// all lanes of one warp: fill the stage of burst b of (batch-relative) frame fr
 	auto issue_burst = [&](long long fr, int b) {
 		if constexpr (FUSED) {
 			const int lane = t & 31;
-			const int s = b % 3;
+			const int s = b % NST;
 			mbar_wait(emptyb + s, ((fullph >> s) & 1u) ^ 1u);
 			if (lane == 0) mbar_expect_tx(fullb + s, SB);
 			__syncwarp();
@@ -557,7 +566,10 @@ wf_fft2_kernel(const Wf2Params p)
 			mbar_init(stashfree, T / 32);
 		}
 		__syncthreads();
-		if (t < 32) issue_burst(f0 >> FLA, 0);
+		if (t < 32) {
+#pragma unroll
+			for (int b = 0; b < ND && b < NB; b++) issue_burst(f0 >> FLA, b);
+		}
 	}
 
 #pragma unroll 1
@@ -610,18 +622,18 @@ wf_fft2_kernel(const Wf2Params p)
 					raw_t raw[2 * HP][2];
 					float wv[2 * HP][2];
 					if (b == 0) {
-						// the stash of the previous frame has been read by every warp: bursts 1, 2 may land in it
+						// the stash of the previous frame has been read by every warp: bursts ND .. NST-1 may land in it
 						if (t < 32) {
 							mbar_wait(stashfree, stashph);
-							if (NB > 1) issue_burst(f >> FLA, 1);
-							if (NB > 2) issue_burst(f >> FLA, 2);
+#pragma unroll
+							for (int b2 = ND; b2 < NST && b2 < NB; b2++) issue_burst(f >> FLA, b2);
 						}
 						stashph ^= 1u;
-					} else if (b + 2 < NB && (t >> 5) == b % (T / 32)) {
-						issue_burst(f >> FLA, b + 2);
+					} else if (b + NST - 1 < NB && (t >> 5) == b % (T / 32)) {
+						issue_burst(f >> FLA, b + NST - 1);      // into the stage burst b - 1 has just left
 					}
 					ptxas_fence(p.stagger & 1);
-					const int s = b % 3;
+					const int s = b % NST;
 					mbar_wait(fullb + s, (fullph >> s) & 1u);
 					fullph ^= 1u << s;
 					{
@@ -776,7 +788,10 @@ wf_fft2_kernel(const Wf2Params p)
 		if constexpr (FUSED) {
 			// every warp is through the load phase of this frame: the ring's own stages can take the first
 			// steps of the next frame now, a whole frame ahead of their use
-			if (t < 32 && (f & (FNA - 1)) == 0 && f + FNA < f1) issue_burst((f >> FLA) + 1, 0);
+			if (t < 32 && (f & (FNA - 1)) == 0 && f + FNA < f1) {
+#pragma unroll
+				for (int b = 0; b < ND && b < NB; b++) issue_burst((f >> FLA) + 1, b);
+			}
 		}
 
 		// every thread has consumed the ring for this frame: fetch the next frame's new samples

@@ -3,8 +3,8 @@ mkdir -p gpurun_out
 timeout 600 python -m pytest tests/test_gpu_parity.py tests/test_zz_no_alloc.py -x -q -m gpu 2>&1 | tail -4
 timeout 200 python tools/stress_determinism.py 2>&1 | tail -3
 for rep in 1 2; do
-for v in nowin ft; do
-  if [ $v = nowin ]; then export RO_CUDA_LIB=$PWD/radio_observer_b200/csrc/_obj/libro_cuda_nowin.so; else unset RO_CUDA_LIB; fi
+for v in ring3 ft; do
+  if [ $v = ring3 ]; then export RO_CUDA_LIB=$PWD/radio_observer_b200/csrc/_obj/libro_cuda_r3.so; else unset RO_CUDA_LIB; fi
   for fmt in int16 float32; do
   echo "## variant $v-$fmt rep $rep"
   timeout 300 python tools/sweep.py --lo 15 --hi 15 --fmt $fmt | python -c "
