@@ -299,6 +299,18 @@ __host__ __device__ constexpr int wf2_tmem_cols()
 	return wf2_tmem_cols_of(LOG2N, (1 << LOG2N) / P, mode_is_split(MODE));
 }
 
+// MODE_SPLIT, 16k items: rows n1 = 0 .. SPLIT_LROWS-1 (4 KB each) of the NEXT item are brought into shared memory by
+// cp.async.bulk while this one is transformed (see the load stage); 16 rows fit the magnitude stash, which the
+// four-class stores leave idle, 8 more take the 32 KB that were free.  -DRO_SPLIT_LROWS=0: off (A/B).
+#ifndef RO_SPLIT_LROWS
+#define RO_SPLIT_LROWS 24
+#endif
+template <int LOG2N, int P, int R3, int MODE>
+__host__ __device__ constexpr int wf2_split_lrows()
+{
+	return (MODE == MODE_SPLIT && LOG2N == 14 && P == 32 && R3 == 16) ? RO_SPLIT_LROWS : 0;
+}
+
 // bytes of dynamic shared memory the kernel needs
 template <int LOG2N, int P, int R3, int MODE>
 constexpr size_t wf2_smem_bytes()
@@ -307,7 +319,8 @@ constexpr size_t wf2_smem_bytes()
 	constexpr size_t PAD1 = (R3 < 16 && !(R3 == 8 && P == 32)) ? R3 : 0;   // 8k: swizzled instead of padded, see the kernel
 	return sizeof(c64) * (N + P * PAD1) + (mode_is_split(MODE) ? 0 : sizeof(float) * (N / 2)) + 32 +
 	       (MODE == MODE_STAGED ? 4 * N : 0) + (mode_is_split(MODE) && P / R3 >= 2 ? 4 * N : 0) +
-	       (mode_is_fused(MODE) ? FUSED_RING_BYTES + FUSED_BAR_BYTES : 0);
+	       (mode_is_fused(MODE) ? FUSED_RING_BYTES + FUSED_BAR_BYTES : 0) +
+	       (wf2_split_lrows<LOG2N, P, R3, MODE>() > 16 ? sizeof(c64) * (N / P) * (wf2_split_lrows<LOG2N, P, R3, MODE>() - 16) : 0);
 }
 
 template <int LOG2N, int P, int R3, int MODE, bool GAIN, int MINB>
@@ -359,6 +372,9 @@ wf_fft2_kernel(const Wf2Params p)
 	// The host never asks for more resident CTAs than 512 columns allow (v2_tmem_cols, ro_cuda.cu).
 	constexpr bool TW_TMEM = RO_TW_TMEM && !SPLIT && wf2_tmem_cols<LOG2N, P, MODE>() > 0;
 	constexpr bool USE_TMEM = SPLIT_TMEM || FUSED_TMEM || TW_TMEM;
+	// rows of the next item prefetched into shared memory (needs the four-class stores: p.pair == 2)
+	constexpr int LROWS = SPLIT_TMEM ? wf2_split_lrows<LOG2N, P, R3, MODE>() : 0;
+	static_assert(SPLIT_TMEM || wf2_split_lrows<LOG2N, P, R3, MODE>() == 0, "the landing area is the stash: parked magnitudes must be in tensor memory");
 	constexpr int TMEM_COLS = wf2_tmem_cols<LOG2N, P, MODE>();
 	constexpr int TMEM_T = (1 << LOG2N) / P;                                                   // threads of the CTA
 	constexpr int TMEM_PER_LEVEL = (TMEM_T >= 128) ? TMEM_COLS / (TMEM_T / 128) : TMEM_COLS;  // columns of one thread
@@ -436,6 +452,22 @@ wf_fft2_kernel(const Wf2Params p)
 			bulk_g2s(reinterpret_cast<unsigned char *>(ring) + o, src + o, CHUNK < 4u * N - o ? CHUNK : 4u * N - o, mbar);
 	}
 	unsigned int parity = 0;
+	// MODE_SPLIT, 16k: rows 0 .. LROWS-1 of item f into the landing area behind mbar + 4 (the magnitude stash of the
+	// other split instantiations: here parked magnitudes live in tensor memory, pairs and fours alike)
+	constexpr bool prefetch_rows = LROWS > 0;
+	auto fetch_rows = [&](long long f) {
+		if constexpr (LROWS > 0) {
+			asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+			constexpr unsigned int BYTES = (unsigned int)LROWS * (unsigned int)M * 8u;
+			mbar_expect_tx(mbar, BYTES);
+			const unsigned char *src = iq8 + 8 * f * N;
+			unsigned char *dst = reinterpret_cast<unsigned char *>(mbar + 4);
+#pragma unroll 1
+			for (unsigned int o = 0; o < BYTES; o += CHUNK)
+				bulk_g2s(dst + o, src + o, CHUNK < BYTES - o ? CHUNK : BYTES - o, mbar);
+		}
+	};
+	if (prefetch_rows && t == 0) fetch_rows(f0);
 
 	// per-thread twiddle bases, fixed for the life of the CTA
 	c64 b1[LP], b2[LP];
@@ -715,10 +747,24 @@ wf_fft2_kernel(const Wf2Params p)
 			}
 		} else if (SPLIT) {
 			const unsigned long long *src = reinterpret_cast<const unsigned long long *>(p.iq) + f * N;
+			if constexpr (prefetch_rows) {
+				// The first LROWS rows of this item were fetched by cp.async.bulk during the previous item's passes 2
+				// and 3; the rest comes by LDG as before, issued first so that its latency passes behind the LDS.
+				const c64 *land = reinterpret_cast<const c64 *>(mbar + 4);
+				ptxas_fence(p.stagger & 1);
+#pragma unroll
+				for (int n1 = LROWS; n1 < R1; n1++) v[n1] = __ldg(src + n1 * M + t);
+				mbar_wait(mbar, parity);
+				parity ^= 1u;
+#pragma unroll
+				for (int n1 = 0; n1 < LROWS; n1++) v[n1] = land[n1 * M + t];
+				ptxas_fence(p.stagger & 1);
+			} else {
 			ptxas_fence(p.stagger & 1);
 #pragma unroll
 			for (int n1 = 0; n1 < R1; n1++) v[n1] = __ldg(src + n1 * M + t);
 			ptxas_fence(p.stagger & 1);
+			}
 			// (prefetching the next item of the scratch into L2 here measured 12 % SLOWER, and bringing it into S
 			// with cp.async.bulk while the previous item is in pass 3 -- S is idle then, and thread t reads and writes
 			// the same column in pass 1 -- 10 % slower at 64k, 8 % at 128k: profiles/r02_split_tma_tmem_ab.txt.
@@ -793,6 +839,9 @@ wf_fft2_kernel(const Wf2Params p)
 				for (int b = 0; b < ND && b < NB; b++) issue_burst((f >> FLA) + 1, b);
 			}
 		}
+
+		// MODE_SPLIT: every thread has read the landing area: the next item's rows may come
+		if (LROWS > 0 && prefetch_rows && t == 0 && f + 1 < f1) fetch_rows(f + 1);
 
 		// every thread has consumed the ring for this frame: fetch the next frame's new samples
 		if (STAGE && t == 0 && f + 1 < f1) {
@@ -953,17 +1002,30 @@ wf_fft2_kernel(const Wf2Params p)
 					// parks its magnitudes in a thread-private slice of shared memory, and the odd class
 					// that the same thread transforms next stores both: bins Na*k + r - 1, Na*k + r.
 					float *stash = reinterpret_cast<float *>(mbar + 4);
+					float evt[SPLIT_TMEM ? 32 : 1];            // SPLIT_TMEM: the even class waits in tensor memory, [k3][c]
 					if ((r & 1) == 0) {
+						if constexpr (SPLIT_TMEM) {
+#pragma unroll
+							for (int g = 0; g < R3 / 4; g++) {
+								float pv[8];
+#pragma unroll
+								for (int i = 0; i < 4; i++) { pv[2 * i] = mag[4 * g + i][0]; pv[2 * i + 1] = mag[4 * g + i][1 % G]; }
+								tmem_st8(tmem + (unsigned int)(8 * g), pv);
+							}
+							tmem_wait_st();
+						} else {
 #pragma unroll
 						for (int k3 = 0; k3 < R3; k3++)
 #pragma unroll
 							for (int c = 0; c < G; c++) stash[(k3 * G + c) * T + t] = mag[k3][c];
+						}
 					} else {
+						if constexpr (SPLIT_TMEM) tmem_ld32(tmem, reinterpret_cast<float (&)[32]>(evt));
 #pragma unroll
 						for (int k3 = 0; k3 < R3; k3++) {
 							float ev[G];
 #pragma unroll
-							for (int c = 0; c < G; c++) ev[c] = stash[(k3 * G + c) * T + t];
+							for (int c = 0; c < G; c++) ev[c] = SPLIT_TMEM ? evt[(k3 * G + c) % (SPLIT_TMEM ? 32 : 1)] : stash[(k3 * G + c) * T + t];
 							const int k = k3 * (N / R3) + G * t;
 							if (G == 2 && la == 1) {
 								// fused 32k: evict-first stores (STG.E.EF), so that the rows do not push the overlapped input
