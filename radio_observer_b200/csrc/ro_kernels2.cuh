@@ -38,7 +38,7 @@ namespace ro {
 #define RO_TRACE_NP 20
 static __device__ unsigned long long ro_trace_buf[2 * RO_TRACE_NF * 16 * RO_TRACE_NP];
 #define RO_TP(i) do { \
-	if (MODE == MODE_STAGED && LOG2N == 14 && (t & 31) == 0 && f - f0 >= RO_TRACE_F0 && f - f0 < RO_TRACE_F0 + RO_TRACE_NF && \
+	if ((MODE == MODE_STAGED || MODE == MODE_SPLIT) && LOG2N == 14 && (t & 31) == 0 && f - f0 >= RO_TRACE_F0 && f - f0 < RO_TRACE_F0 + RO_TRACE_NF && \
 	    (blockIdx.x == 0 || blockIdx.x == 73)) \
 		ro_trace_buf[(((blockIdx.x ? 1 : 0) * RO_TRACE_NF + (int)(f - f0) - RO_TRACE_F0) * 16 + (t >> 5)) * RO_TRACE_NP + (i)] = clock64(); \
 } while (0)
@@ -455,6 +455,9 @@ wf_fft2_kernel(const Wf2Params p)
 	// MODE_SPLIT, 16k: rows 0 .. LROWS-1 of item f into the landing area behind mbar + 4 (the magnitude stash of the
 	// other split instantiations: here parked magnitudes live in tensor memory, pairs and fours alike)
 	constexpr bool prefetch_rows = LROWS > 0;
+	// Measured and not kept (B200, profiles/r02_split_late_rows_ab.txt, r02_split_deferred_stores_ab.txt): the last
+	// R1 - LROWS rows by a second bulk copy straight into S once every thread holds its pass-3 inputs of the item
+	// before (-13 %); the fourth class's row stores deferred into the next item, half in front of each CTA barrier (-4 %).
 	auto fetch_rows = [&](long long f) {
 		if constexpr (LROWS > 0) {
 			asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -747,6 +750,7 @@ wf_fft2_kernel(const Wf2Params p)
 			}
 		} else if (SPLIT) {
 			const unsigned long long *src = reinterpret_cast<const unsigned long long *>(p.iq) + f * N;
+			RO_TP(0);
 			if constexpr (prefetch_rows) {
 				// The first LROWS rows of this item were fetched by cp.async.bulk during the previous item's passes 2
 				// and 3; the rest comes by LDG as before, issued first so that its latency passes behind the LDS.
@@ -759,6 +763,7 @@ wf_fft2_kernel(const Wf2Params p)
 #pragma unroll
 				for (int n1 = 0; n1 < LROWS; n1++) v[n1] = land[n1 * M + t];
 				ptxas_fence(p.stagger & 1);
+				RO_TP(1);
 			} else {
 			ptxas_fence(p.stagger & 1);
 #pragma unroll
@@ -1056,6 +1061,7 @@ wf_fft2_kernel(const Wf2Params p)
 					}
 				}
 				}
+				if (MODE == MODE_SPLIT) RO_TP(16);
 				if constexpr (FUSED) {
 					// the last class of the frame has read the stash: its 64 KB may stage the next frame
 					if (r == FNA - 1) {

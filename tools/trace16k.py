@@ -29,6 +29,7 @@ NAMES = ["frame start", "samples landed (TMA)", "loaded + windowed", "pass 1 don
 
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--bins", type=int, default=16384, help="16384: the staged kernel; 65536 ..: the split path's 16k items")
     ap.add_argument("--overlap", type=int, default=12288)
     ap.add_argument("--log2-samples", type=int, default=26)
     ap.add_argument("--tuning", type=int, default=0)
@@ -41,9 +42,9 @@ def main():
     iq = np.random.default_rng(5).integers(-3000, 3000, size=2 * S, dtype=np.int16)
     d_iq = DeviceBuffer(iq.nbytes)
     d_iq.upload(iq)
-    wf = ro.Waterfall(16384, a.overlap, sample_rate=96000, in_format=ro.IN_INT16, tuning=a.tuning)
+    wf = ro.Waterfall(a.bins, a.overlap, sample_rate=96000, in_format=ro.IN_INT16, tuning=a.tuning)
     F = wf.frame_count(S)
-    d_rows = DeviceBuffer(4 * 16384 * F)
+    d_rows = DeviceBuffer(4 * a.bins * F)
     for _ in range(3):
         wf.process_resident(d_iq.ptr, S, d_rows.ptr, None, sync=True)
     wf.set_profiling(True)
