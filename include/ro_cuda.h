@@ -13,6 +13,13 @@
  * negative RO_E_* code on failure; ro_last_error() gives the message of the
  * last failure on the calling thread.  No C++ exception crosses this ABI.
  * A handle is single-producer: call it from one thread at a time.
+ *
+ * Device resources beyond global memory: the kernels for frames of 16384 points and more (one CTA per SM,
+ * about 229 KB of shared memory each) allocate all 512 columns of the SM's tensor memory for their lifetime
+ * and use them as thread-private storage (twiddle tables, parked residue classes and magnitudes; no
+ * tcgen05.mma).  Another kernel that wants tensor memory on the same SM at the same time (a cuBLAS / CUTLASS
+ * GEMM of the same process on another stream) waits in its tcgen05.alloc until such a CTA exits, and the
+ * other way round: it costs overlap, never progress.
  */
 #ifndef RO_CUDA_H
 #define RO_CUDA_H

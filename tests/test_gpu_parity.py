@@ -192,6 +192,41 @@ def test_long_frames_four_classes_stored_together(bins, hop, fmt, iq_gain):
     assert_rows_close(rows, ref, f"{fmt} quads N={bins} hop={hop}")
 
 
+@pytest.mark.timeout(180)
+def test_two_handles_in_flight_on_one_device():
+    """Two handles whose kernels each take all of an SM's tensor memory (a 16k stream and a 64k one), asynchronous
+    calls on their own streams issued back to back several times, waited for at the end: the rows are the ones each
+    handle gives alone.  (Their CTAs cannot share an SM -- shared memory -- so neither ever waits for the other's
+    tensor memory; a regression there would hang, hence the timeout.)"""
+    cases = [(16384, 12288, 300), (65536, 49152, 160)]
+    hs, bufs, alone = [], [], []
+    try:
+        for bins, overlap, frames in cases:
+            hop = bins - overlap
+            n = bins + (frames - 1) * hop
+            iq = station_iq(n, 96000, seed=bins + 5)
+            wf = ro.Waterfall(bins, overlap, sample_rate=96000, in_format=ro.IN_INT16)
+            d_in, d_rows = DeviceBuffer(iq.nbytes), DeviceBuffer(4 * bins * frames)
+            d_in.upload(iq)
+            assert wf.process_resident(d_in.ptr, n, d_rows.ptr, None) == frames
+            alone.append(d_rows.download(np.float32, frames * bins))
+            ro.load_library().ro_dev_memset(0, d_rows.ptr, 0, d_rows.nbytes)
+            hs.append((wf, n, frames, bins))
+            bufs.append((d_in, d_rows))
+        for _ in range(4):
+            for (wf, n, frames, bins), (d_in, d_rows) in zip(hs, bufs):
+                assert wf.process_resident(d_in.ptr, n, d_rows.ptr, None, sync=False) == frames
+        for (wf, n, frames, bins), (d_in, d_rows), ref in zip(hs, bufs, alone):
+            wf.sync()
+            assert np.array_equal(d_rows.download(np.float32, frames * bins), ref)
+    finally:
+        for wf, *_ in hs:
+            wf.close()
+        for d_in, d_rows in bufs:
+            d_in.free()
+            d_rows.free()
+
+
 def test_complex64_input_is_narrowed_like_float32():
     bins, overlap = 4096, 3072
     spec = synth.SynthSpec(sample_rate=48000, n_samples=bins * 4, seed=3)
