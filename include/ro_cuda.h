@@ -89,7 +89,7 @@ typedef struct ro_wf_config {
 } ro_wf_config;
 
 /* tuning bits: A/B switches for measurements and tests; results do not depend on them */
-#define RO_TUNE_NO_FUSED   1   /* 32768-point frames through the split path instead of the fused kernel */
+#define RO_TUNE_NO_FUSED   1   /* 32768- and 65536-point frames through the split path instead of the fused kernels */
 #define RO_TUNE_NO_PAIR    2   /* split path: every residue class stores its own bins (no paired stores) */
 #define RO_TUNE_NO_CHAIN   4   /* the warps of a scheduler do not take turns with their shared-memory load bursts */
 

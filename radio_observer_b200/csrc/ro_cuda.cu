@@ -340,7 +340,8 @@ int launch_fft(ro_wf *h, cudaStream_t s, const void *d_iq, float *d_rows, long l
 		return fail(RO_E_INVALID, "float32 device input must be 8-byte aligned");
 	// the fused long-frame kernel stages samples with cp.async.bulk: 16-byte aligned frame starts
 	if (h->fused_ok && ((uintptr_t)d_iq & 15) == 0 && ((long long)h->hop * h->in_bytes) % 16 == 0) {
-		h->last_kernel = h->fmt == ro::FMT_FLOAT32 ? "wf_fft2_kernel<14,32,16,MODE_FUSED1_F32> (2 x 16k per frame, TMA-staged load phase)"
+		h->last_kernel = h->log2na == 2 ? "wf_fft2_kernel<14,32,16,MODE_FUSED2> (4 x 16k per frame, TMA-staged load phase)"
+		               : h->fmt == ro::FMT_FLOAT32 ? "wf_fft2_kernel<14,32,16,MODE_FUSED1_F32> (2 x 16k per frame, TMA-staged load phase)"
 		                                           : "wf_fft2_kernel<14,32,16,MODE_FUSED1> (2 x 16k per frame, TMA-staged load phase)";
 		const long long cap = h->v2f_grid_cap;
 		const long long fpc = (n_frames + cap - 1) / cap;          // contiguous frames per CTA
@@ -352,7 +353,7 @@ int launch_fft(ro_wf *h, cudaStream_t s, const void *d_iq, float *d_rows, long l
 			CU(cudaEventRecord(e0, s));
 		}
 		CU(ro::v2_launch_fused(h->v2f, grid, s, d_iq, h->d_window, h->d_tw, h->d_tw_nb, h->d_fscratch, d_rows,
-		                       row_stride, n_frames, h->hop, fpc, (float)h->cfg.iq_gain, 1, h->stagger));
+		                       row_stride, n_frames, h->hop, fpc, (float)h->cfg.iq_gain, 1, h->stagger, h->log2na));
 		h->launches++;
 		if (h->profiling) {
 			CU(cudaEventRecord(e1, s));
@@ -712,8 +713,10 @@ extern "C" int ro_wf_create(const ro_wf_config *cfg, ro_wf **out)
 		}
 	}
 	h->fused_ok = false;
-	if (h->split_ok && sym && log2nb == 14 && h->log2na == 1 && !(cfg->tuning & RO_TUNE_NO_FUSED) &&
-	    (h->fmt == ro::FMT_INT16 ? ro::v2_pick(14, ro::V2_FUSED1, false, &h->v2f) : ro::v2_pick_fused_f32(&h->v2f))) {
+	// 32k frames (int16, float32) and 64k frames (int16) run in ONE kernel when the window is symmetric
+	if (h->split_ok && sym && log2nb == 14 && !(cfg->tuning & RO_TUNE_NO_FUSED) &&
+	    ((h->log2na == 1 && (h->fmt == ro::FMT_INT16 ? ro::v2_pick(14, ro::V2_FUSED1, false, &h->v2f) : ro::v2_pick_fused_f32(&h->v2f))) ||
+	     (h->log2na == 2 && h->fmt == ro::FMT_INT16 && ro::v2_pick(14, ro::V2_FUSED2, false, &h->v2f)))) {
 		CUH(cudaFuncSetAttribute(h->v2f.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->v2f.smem));
 		int occ4 = 0;
 		CUH(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ4, h->v2f.fn, h->v2f.threads, h->v2f.smem));

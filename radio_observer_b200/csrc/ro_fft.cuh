@@ -50,6 +50,21 @@ __host__ __device__ constexpr float cw64(int j)
 }
 __host__ __device__ constexpr float sw64(int j) { return j <= 16 ? cw64(16 - j) : cw64(j - 16); }
 
+// cos(2*pi*j/128), sin(2*pi*j/128) for j = 0..127 (table for the first quadrant, rounded once)
+__host__ __device__ constexpr float cw128(int j)
+{
+	constexpr float T[33] = {1.000000000e+00f, 9.987954497e-01f, 9.951847196e-01f, 9.891765118e-01f, 9.807852507e-01f,
+	                         9.700312614e-01f, 9.569403529e-01f, 9.415440559e-01f, 9.238795042e-01f, 9.039893150e-01f,
+	                         8.819212914e-01f, 8.577286005e-01f, 8.314695954e-01f, 8.032075167e-01f, 7.730104327e-01f,
+	                         7.409511209e-01f, 7.071067691e-01f, 6.715589762e-01f, 6.343932748e-01f, 5.956993103e-01f,
+	                         5.555702448e-01f, 5.141027570e-01f, 4.713967443e-01f, 4.275550842e-01f, 3.826834261e-01f,
+	                         3.368898630e-01f, 2.902846634e-01f, 2.429801822e-01f, 1.950903237e-01f, 1.467304677e-01f,
+	                         9.801714122e-02f, 4.906767607e-02f, 0.0f};
+	const int k = j & 127;
+	return k <= 32 ? T[k] : k <= 64 ? -T[64 - k] : k <= 96 ? -T[k - 64] : T[128 - k];
+}
+__host__ __device__ constexpr float sw128(int j) { return cw128(j + 96); }      // sin(x) = cos(x - pi/2) = cos(x + 3*pi/2)
+
 __host__ __device__ constexpr int ilog2(int v) { return v <= 1 ? 0 : 1 + ilog2(v >> 1); }
 
 __host__ __device__ constexpr int bitrev(int v, int bits)

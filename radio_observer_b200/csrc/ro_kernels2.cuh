@@ -75,9 +75,11 @@ enum { MODE_DIRECT = 0,   // int16 I/Q read from global memory, row = item
                           // radix-Na step done): item = frame*Na + r, output k is bin Na*k + r
        MODE_FUSED1 = 3,   // like MODE_SPLIT with Na = 2, but the radix-2 step is done here, per frame, by the
                           // thread that needs its results: no scratch round trip through HBM
+       MODE_FUSED2 = 4,   // the same for Na = 4 (64k frames): radix-4 step here, classes 1 and 2 wait in tensor memory,
+                          // class 3 in a CTA-private slice of global memory, four classes stored together
        MODE_DIRECT_F32 = 5,   // MODE_DIRECT for float32 I/Q (the reference's raw-TCP / JACK encoding)
        MODE_FUSED1_F32 = 6 }; // MODE_FUSED1 for float32 I/Q
-__host__ __device__ constexpr bool mode_is_fused(int m) { return m == MODE_FUSED1 || m == MODE_FUSED1_F32; }
+__host__ __device__ constexpr bool mode_is_fused(int m) { return m == MODE_FUSED1 || m == MODE_FUSED1_F32 || m == MODE_FUSED2; }
 __host__ __device__ constexpr bool mode_is_split(int m) { return m == MODE_SPLIT || mode_is_fused(m); }
 __host__ __device__ constexpr bool mode_is_f32(int m) { return m == MODE_DIRECT_F32 || m == MODE_FUSED1_F32; }
 // MODE_FUSED*: bytes of the raw-sample / window staging ring beside the 64 KB stash, and of its barriers
@@ -260,6 +262,14 @@ __device__ __forceinline__ void tmem_ld_f(unsigned int taddr, float (&v)[4])
 	asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(taddr) : "memory");
 	v[0] = __uint_as_float(a); v[1] = __uint_as_float(b); v[2] = __uint_as_float(c); v[3] = __uint_as_float(d);
 }
+__device__ __forceinline__ void tmem_ld_f(unsigned int taddr, float (&v)[8])
+{
+	unsigned int r[8];
+	asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+	             : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "r"(taddr) : "memory");
+#pragma unroll
+	for (int i = 0; i < 8; i++) v[i] = __uint_as_float(r[i]);
+}
 __device__ __forceinline__ void tmem_st_f(unsigned int taddr, const float (&v)[8])
 {
 	tmem_st8(taddr, v);
@@ -337,7 +347,7 @@ wf_fft2_kernel(const Wf2Params p)
 	constexpr bool FIN32 = MODE == MODE_FUSED1_F32;   // fused, float32 input
 	constexpr bool FUSED = mode_is_fused(MODE);
 	constexpr bool F32 = MODE == MODE_DIRECT_F32;
-	constexpr int FLA = FUSED ? 1 : 0;   // log2(Na) of the fused modes
+	constexpr int FLA = MODE == MODE_FUSED2 ? 2 : FUSED ? 1 : 0;   // log2(Na) of the fused modes
 	constexpr bool SPLIT = MODE == MODE_SPLIT || FUSED;
 	// MODE_SPLIT, 16k items, Na >= 4: the magnitudes of three residue classes wait in tensor memory for the
 	// fourth, see the store stage.  -DRO_SPLIT_TMEM=0 for the A/B.
@@ -357,7 +367,7 @@ wf_fft2_kernel(const Wf2Params p)
 #ifndef RO_FUSED_WIN_TMEM
 #define RO_FUSED_WIN_TMEM 1
 #endif
-	constexpr bool WIN_TMEM = RO_FUSED_WIN_TMEM && FUSED_TMEM;
+	constexpr bool WIN_TMEM = RO_FUSED_WIN_TMEM && FUSED_TMEM && MODE != MODE_FUSED2;   // Na = 4: both halves hold parked classes
 	// One-kernel modes, 16k: the 31 + 31 twiddle factors a thread multiplies its pass-1 and pass-2 outputs by are
 	// the same for every frame (W_N^(t*k1), W_512^(n3*k2)).  They used to be rebuilt from five table entries each
 	// in every frame (26 complex multiplications per pass before the 31 that apply them: 104 of the 824 packed
@@ -550,14 +560,16 @@ wf_fft2_kernel(const Wf2Params p)
 	// b + NST - 1 when warp b % 16 starts burst b (into the stage burst b - 1 has just left); the
 	// empty-barrier parity to wait for is the complement of the consumer's own phase bit of that stage
 	// (its last use has been consumed).
-	static_assert(!FUSED || FLA == 1, "the fused kernel does the radix-2 step only");
+	static_assert(!FUSED || FLA == 1 || (FLA == 2 && FUSED_TMEM), "the fused kernels do the radix-2 step, or the radix-4 step with tensor memory");
 	constexpr int FNA = 1 << FLA;
 	constexpr int RAWB = FIN32 ? 8 : 4;
-	constexpr int HP = FIN32 ? 1 : 2;                              // positions per burst from each end
+	constexpr int HP = (FIN32 || FLA == 2) ? 1 : 2;                // positions per burst from each end
 	constexpr unsigned int RUN_RAW = (unsigned int)(HP * M) * RAWB, RUN_WIN = (unsigned int)(HP * M) * 4u;
 	// bytes per stage: four sample runs, and unless the window waits in tensor memory two window runs:
 	// 16 KB (24 KB with window) for int16, 16 KB (20 KB) for float32
-	constexpr unsigned int SB = 4u * RUN_RAW + (WIN_TMEM ? 0u : 2u * RUN_WIN);
+	// (Na = 4: eight sample runs and four window runs -- q = 0, 1 at either end; q = 2, 3 are their mirror images --
+	// of one position each: 24 KB)
+	constexpr unsigned int SB = 2u * FNA * RUN_RAW + (WIN_TMEM ? 0u : (unsigned int)FNA * RUN_WIN);
 	// ring: ND stages of memory of their own (filled a whole frame ahead), NS more in the magnitude stash (filled at
 	// the start of the load phase); 1 + 2 with the window runs in the bursts, 2 + 4 without.  -DRO_FUSED_RING3=1: 1 + 2.
 #ifndef RO_FUSED_RING3
@@ -582,15 +594,16 @@ wf_fft2_kernel(const Wf2Params p)
 			mbar_wait(emptyb + s, ((fullph >> s) & 1u) ^ 1u);
 			if (lane == 0) mbar_expect_tx(fullb + s, SB);
 			__syncwarp();
-			if (lane < (WIN_TMEM ? 4 : 6)) {
+			if (lane < (WIN_TMEM ? 2 * FNA : 3 * FNA)) {
 				const int pos0 = (lane & 1) ? R1 - (b + 1) * HP : b * HP;      // odd lanes: the high end
 				unsigned char *dst = stage_ptr(s);
-				if (lane < 4)      // sample run q = lane / 2
+				if (lane < 2 * FNA)      // sample run q = lane / 2
 					bulk_g2s(dst + lane * RUN_RAW,
 					         reinterpret_cast<const unsigned char *>(p.raw) + (fr * hop + (long long)(lane >> 1) * N + pos0 * M) * RAWB,
 					         RUN_RAW, fullb + s);
-				else               // window run of the first half of the table
-					bulk_g2s(dst + 4 * RUN_RAW + (lane & 1) * RUN_WIN, p.window_full + pos0 * M, RUN_WIN, fullb + s);
+				else                     // window run q = (lane - 2*Na) / 2 of the first half of the table
+					bulk_g2s(dst + 2 * FNA * RUN_RAW + (lane - 2 * FNA) * RUN_WIN,
+					         p.window_full + (long long)((lane - 2 * FNA) >> 1) * N + pos0 * M, RUN_WIN, fullb + s);
 			}
 			__syncwarp();
 		}
@@ -645,17 +658,22 @@ wf_fft2_kernel(const Wf2Params p)
 			constexpr int NA = FNA;
 			constexpr int NBIG = N << FLA;
 			const int r = (int)(f & (NA - 1));
-			unsigned long long *scr = p.scratch + (size_t)blockIdx.x * (NA - 1) * N;
+			// Na = 2: one class parked (tensor memory, or (Na-1) slices of global memory without it); Na = 4: classes
+			// 1 and 2 in the two halves of the thread's tensor memory, class 3 in ONE slice of global memory
+			unsigned long long *scr = p.scratch + (size_t)blockIdx.x * (FLA == 2 ? 1 : NA - 1) * N;
 			if (r == 0) {
 				typedef typename raw_word<FIN32>::type raw_t;
 				const raw_t *src = reinterpret_cast<const raw_t *>(p.raw) + (f >> FLA) * hop;
-				// The twiddle W_{2N}^m, m = n1*M + t, is W_{2N}^t (loaded once per frame) times the compile-time
-				// constant W_{2N/M}^{n1} = W_64^{n1}.
-				const c64 wt1 = __ldg(reinterpret_cast<const unsigned long long *>(p.tw_big) + t);
+				// The twiddle W_{Na*N}^(m*r), m = n1*M + t, is W_{Na*N}^(t*r) (loaded once per frame) times the
+				// compile-time constant W_{Na*N/M}^(n1*r) = W_64^n1 (Na = 2), W_128^(n1*r) (Na = 4).
+				const unsigned long long *twb = reinterpret_cast<const unsigned long long *>(p.tw_big);
+				const c64 wt1 = __ldg(twb + t);
+				c64 wt2 = wt1, wt3 = wt1;
+				if (FLA == 2) { wt2 = __ldg(twb + 2 * t); wt3 = __ldg(twb + 3 * t); }
 #pragma unroll
 				for (int b = 0; b < NB; b++) {
-					raw_t raw[2 * HP][2];
-					float wv[2 * HP][2];
+					raw_t raw[2 * HP][NA];
+					float wv[2 * HP][NA];
 					if (b == 0) {
 						// the stash of the previous frame has been read by every warp: bursts ND .. NST-1 may land in it
 						if (t < 32) {
@@ -674,7 +692,7 @@ wf_fft2_kernel(const Wf2Params p)
 					{
 						const unsigned char *st = stage_ptr(s);
 						const raw_t *rr = reinterpret_cast<const raw_t *>(st);
-						const float *wl = reinterpret_cast<const float *>(st + 4 * RUN_RAW), *wh = wl + HP * M;
+						const float *wl = reinterpret_cast<const float *>(st + 2 * NA * RUN_RAW), *wh = wl + HP * M;
 						float wlo[2 * HP], whi[2 * HP];         // WIN_TMEM: [position][q] of the low and the high run
 						if constexpr (WIN_TMEM) {
 							tmem_ld_f(tmem + 64u + (unsigned int)(2 * b * HP), wlo);
@@ -683,15 +701,22 @@ wf_fft2_kernel(const Wf2Params p)
 #pragma unroll
 						for (int j = 0; j < HP; j++) {
 							// j: low position b*HP + j;  HP + j: high position R1 - (b+1)*HP + j
-							raw[j][0] = rr[0 * HP * M + j * M + t];
-							raw[HP + j][0] = rr[1 * HP * M + j * M + t];
-							raw[j][1] = rr[2 * HP * M + j * M + t];
-							raw[HP + j][1] = rr[3 * HP * M + j * M + t];
+#pragma unroll
+							for (int q = 0; q < NA; q++) {
+								raw[j][q] = rr[(2 * q) * HP * M + j * M + t];
+								raw[HP + j][q] = rr[(2 * q + 1) * HP * M + j * M + t];
+							}
 							if constexpr (!WIN_TMEM) {
-								wv[j][0] = wl[j * M + t];
-								wv[HP + j][0] = wh[j * M + t];
-								wv[j][1] = wh[(HP - 1 - j) * M + (M - 1 - t)];
-								wv[HP + j][1] = wl[(HP - 1 - j) * M + (M - 1 - t)];
+								// window runs q = 0 .. Na/2-1 at either end; q >= Na/2 is the mirror image of q' = Na-1-q at
+								// the OTHER end: w[q*N + m] = w[q'*N + (N-1-m)]
+#pragma unroll
+								for (int q = 0; q < NA / 2; q++) {
+									const float *wlq = wl + 2 * q * HP * M, *whq = wlq + HP * M;
+									wv[j][q] = wlq[j * M + t];
+									wv[HP + j][q] = whq[j * M + t];
+									wv[j][NA - 1 - q] = whq[(HP - 1 - j) * M + (M - 1 - t)];
+									wv[HP + j][NA - 1 - q] = wlq[(HP - 1 - j) * M + (M - 1 - t)];
+								}
 							}
 						}
 						if constexpr (WIN_TMEM) {
@@ -704,25 +729,35 @@ wf_fft2_kernel(const Wf2Params p)
 						}
 					}
 					ptxas_fence(p.stagger & 1);
-					c64 y1[2][HP];                     // the odd class at the low and the high positions of this burst
+					c64 y1[2][HP], y2[2][HP];          // classes 1 (and 2) at the low and the high positions of this burst
 #pragma unroll
 					for (int jj = 0; jj < 2 * HP; jj++) {
 						const int n1 = jj < HP ? b * HP + jj : R1 - (b + 1) * HP + (jj - HP);
 						const int m = n1 * M + t;
-						c64 xq[2];
+						c64 xq[NA];
 #pragma unroll
-						for (int q = 0; q < 2; q++)
+						for (int q = 0; q < NA; q++)
 							xq[q] = mul2(add2(raw_to_c64(raw[jj][q]), gain2), pk(wv[jj][q], wv[jj][q]));
-						fft_dif2<2>(xq);
-						xq[1] = cmul2(cmul2(xq[1], wt1), cw64(n1), -sw64(n1));
+						fft_dif2<NA>(xq);                     // class rr is left at xq[bitrev(rr)]
 						v[n1] = xq[0];
-						if (FUSED_TMEM) y1[jj / HP][jj % HP] = xq[1];
-						else scr[m] = xq[1];
+						if constexpr (FLA == 2) {
+							y1[jj / HP][jj % HP] = cmul2(cmul2(xq[2], wt1), cw128(n1), -sw128(n1));
+							y2[jj / HP][jj % HP] = cmul2(cmul2(xq[1], wt2), cw128(2 * n1), -sw128(2 * n1));
+							scr[m] = cmul2(cmul2(xq[3], wt3), cw128(3 * n1), -sw128(3 * n1));
+						} else {
+							xq[1] = cmul2(cmul2(xq[1], wt1), cw64(n1), -sw64(n1));
+							if (FUSED_TMEM) y1[jj / HP][jj % HP] = xq[1];
+							else scr[m] = xq[1];
+						}
 					}
 					if constexpr (FUSED_TMEM) {
-						// columns 2*n1, 2*n1 + 1 of this thread's 128
+						// columns 2*n1, 2*n1 + 1 of this thread's 128 (Na = 4: class 2 in the upper 64)
 						tmem_st_c64(tmem + (unsigned int)(2 * b * HP), y1[0]);
 						tmem_st_c64(tmem + (unsigned int)(2 * (R1 - (b + 1) * HP)), y1[1]);
+						if constexpr (FLA == 2) {
+							tmem_st_c64(tmem + 64u + (unsigned int)(2 * b * HP), y2[0]);
+							tmem_st_c64(tmem + 64u + (unsigned int)(2 * (R1 - (b + 1) * HP)), y2[1]);
+						}
 					}
 					// the values are in registers and used: the stage may be refilled
 					__syncwarp();
@@ -735,13 +770,14 @@ wf_fft2_kernel(const Wf2Params p)
 						asm volatile("prefetch.global.L2 [%0];" :: "l"(nx + o));
 				}
 #endif
-			} else if (FUSED_TMEM) {
+			} else if (FUSED_TMEM && r < 3) {
 				tmem_wait_st();
-				tmem_ld_c64x16(tmem, &v[0]);
-				tmem_ld_c64x16(tmem + 32u, &v[16]);
+				const unsigned int half = r == 2 ? 64u : 0u;
+				tmem_ld_c64x16(tmem + half, &v[0]);
+				tmem_ld_c64x16(tmem + half + 32u, &v[16]);
 				tmem_wait_ld();
 			} else {
-				const unsigned long long *src = scr + (r - 1) * N;
+				const unsigned long long *src = scr + (FLA == 2 ? 0 : r - 1) * N;
 				ptxas_fence(p.stagger & 1);
 #pragma unroll
 				for (int n1 = 0; n1 < R1; n1++) v[n1] = __ldcg(src + n1 * M + t);
@@ -951,7 +987,53 @@ wf_fft2_kernel(const Wf2Params p)
 				const int r = (int)(f & ((1 << la) - 1));
 				float *row = p.rows + (f >> la) * p.row_stride;
 				const int big_mask = (N << la) - 1, big_half = (N << la) >> 1;
-				if (SPLIT_TMEM && p.pair == 2 && la >= 2) {
+				if constexpr (FLA == 2) {
+					// MODE_FUSED2: the four classes of a frame are stored together, 32-byte sectors whole (see the split
+					// path below).  Class 0 waits in the shared-memory stash, classes 1 and 2 in the lower half of the
+					// thread's tensor memory (columns 32*(r-1) + 2*k3 + c), which their own parked inputs have left.
+					float *stash = reinterpret_cast<float *>(mbar + 4);
+					if (r == 0) {
+#pragma unroll
+						for (int k3 = 0; k3 < R3; k3++)
+#pragma unroll
+							for (int c = 0; c < G; c++) stash[(k3 * G + c) * T + t] = mag[k3][c];
+					} else if (r < 3) {
+#pragma unroll
+						for (int g = 0; g < R3 / 4; g++) {
+							float pv[8];
+#pragma unroll
+							for (int i = 0; i < 4; i++) { pv[2 * i] = mag[4 * g + i][0]; pv[2 * i + 1] = mag[4 * g + i][1 % G]; }
+							tmem_st8(tmem + (unsigned int)(32 * (r - 1) + 8 * g), pv);
+						}
+						tmem_wait_st();
+					} else {
+						const int odd = t & 1;
+#pragma unroll
+						for (int g = 0; g < R3 / 4; g++) {
+							float m1[8], m2[8];
+							tmem_ld_f(tmem + (unsigned int)(8 * g), m1);
+							tmem_ld_f(tmem + 32u + (unsigned int)(8 * g), m2);
+							tmem_wait_ld();
+#pragma unroll
+							for (int i = 0; i < 4; i++) {
+								const int k3 = 4 * g + i;
+								const float4 a0 = make_float4(stash[(k3 * G) * T + t], m1[2 * i], m2[2 * i], mag[k3][0]);
+								const float4 a1 = make_float4(stash[(k3 * G + 1 % G) * T + t], m1[2 * i + 1], m2[2 * i + 1], mag[k3][1 % G]);
+								const float4 snd = odd ? a0 : a1;
+								float4 rcv;
+								rcv.x = __shfl_xor_sync(0xffffffffu, snd.x, 1);
+								rcv.y = __shfl_xor_sync(0xffffffffu, snd.y, 1);
+								rcv.z = __shfl_xor_sync(0xffffffffu, snd.z, 1);
+								rcv.w = __shfl_xor_sync(0xffffffffu, snd.w, 1);
+								const int blk = (k3 * (N / R3)) << 2;          // first bin of the k3 block
+								float4 *lo = reinterpret_cast<float4 *>(row + ((blk + 8 * (t & ~1) + big_half) & big_mask) + 4 * odd);
+								float4 *hi = reinterpret_cast<float4 *>(row + ((blk + 8 * (t | 1) + big_half) & big_mask) + 4 * odd);
+								__stcs(lo, odd ? rcv : a0);
+								__stcs(hi, odd ? a1 : rcv);
+							}
+						}
+					}
+				} else if (SPLIT_TMEM && p.pair == 2 && la >= 2) {
 					// Na >= 4.  With pairs a thread wrote 8 bytes of every 4*Na: at Na = 4 half of a 32-byte sector
 					// now and the other half two items later, and every sector of the row made two partial trips
 					// to HBM (ncu, 64k: 243 KB read back and 121 KB written twice per 256 KB row).  Classes r = 4j ..

@@ -41,6 +41,16 @@ bool v2_pick(int log2n, int mode, bool gain, V2Kernel *out)
 		out->fn = (const void *)wf_fft2_kernel<14, 32, 16, MODE_FUSED1, false, 1>;
 		return true;
 	}
+	if (mode == V2_FUSED2) {
+		if (log2n != 14) return false;
+		out->log2n = log2n;
+		out->mode = mode;
+		out->gain = false;
+		out->threads = (1 << 14) / 32;
+		out->smem = wf2_smem_bytes<14, 32, 16, MODE_FUSED2>();
+		out->fn = (const void *)wf_fft2_kernel<14, 32, 16, MODE_FUSED2, false, 1>;
+		return true;
+	}
 	if (mode == V2_SPLIT) {
 		out->log2n = log2n;
 		out->mode = mode;
@@ -86,7 +96,7 @@ bool v2_pick(int log2n, int mode, bool gain, V2Kernel *out)
 
 int v2_tmem_cols(const V2Kernel &k)
 {
-	return wf2_tmem_cols_of(k.log2n, k.threads, k.mode == V2_SPLIT || k.mode == V2_FUSED1 || k.mode == V2_FUSED1_F32);
+	return wf2_tmem_cols_of(k.log2n, k.threads, k.mode == V2_SPLIT || k.mode == V2_FUSED1 || k.mode == V2_FUSED2 || k.mode == V2_FUSED1_F32);
 }
 
 cudaError_t v2_launch(const V2Kernel &k, int grid, cudaStream_t s, const void *d_iq, const float *d_window_half,
@@ -117,9 +127,9 @@ cudaError_t v2_launch(const V2Kernel &k, int grid, cudaStream_t s, const void *d
 cudaError_t v2_launch_fused(const V2Kernel &k, int grid, cudaStream_t s, const void *d_raw, const float *d_window_full,
                             const float2 *d_tw_big, const float2 *d_tw_nb, void *d_scratch, float *d_rows,
                             long long row_stride, long long n_frames, long long hop, long long frames_per_cta,
-                            float iq_gain, int pair, int stagger)
+                            float iq_gain, int pair, int stagger, int log2na)
 {
-	const int la = 1;
+	const int la = log2na;
 	Wf2Params p;
 	p.iq = NULL;
 	p.window_half = NULL;

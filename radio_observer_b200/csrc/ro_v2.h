@@ -5,7 +5,7 @@
 
 namespace ro {
 
-enum { V2_DIRECT = 0, V2_STAGED = 1, V2_SPLIT = 2, V2_FUSED1 = 3, V2_DIRECT_F32 = 5, V2_FUSED1_F32 = 6 };   // = MODE_* of ro_kernels2.cuh
+enum { V2_DIRECT = 0, V2_STAGED = 1, V2_SPLIT = 2, V2_FUSED1 = 3, V2_FUSED2 = 4, V2_DIRECT_F32 = 5, V2_FUSED1_F32 = 6 };   // = MODE_* of ro_kernels2.cuh
 
 struct V2Kernel {
 	const void *fn;      // kernel symbol (for attribute / occupancy queries)
@@ -42,10 +42,11 @@ cudaError_t v2_launch(const V2Kernel &k, int grid, cudaStream_t s, const void *d
 // frame; d_scratch holds grid * 16384 packed complex.  The raw samples and the first half of the window
 // (which must be symmetric) reach shared memory by cp.async.bulk: d_raw and every frame start
 // (hop * bytes per sample) must be 16-byte aligned, rows 16-byte aligned (pair = 1).
+// V2_FUSED2 (frames of 4*16384 points, int16): log2na = 2, d_window_full / d_tw_big of 65536 entries.
 cudaError_t v2_launch_fused(const V2Kernel &k, int grid, cudaStream_t s, const void *d_raw, const float *d_window_full,
                             const float2 *d_tw_big, const float2 *d_tw_nb, void *d_scratch, float *d_rows,
                             long long row_stride, long long n_frames, long long hop, long long frames_per_cta,
-                            float iq_gain, int pair, int stagger);
+                            float iq_gain, int pair, int stagger, int log2na = 1);
 
 // First radix-Na step of frames frame0 .. frame0+n_frames-1 (N = 2^log2n points, Na = 2^log2na)
 // into d_y[n_frames][Na][N/Na] (packed complex float).  f32in: float32 I/Q instead of int16.

@@ -134,8 +134,9 @@ def test_float32_32k_fused_many_frames_per_cta(overlap, iq_gain):
     (65536, "int16", 32768, -3.0), (65536, "float32", 49152, 0.125), (65536, "int16", 65536 - 16381, 0.0),
 ])
 def test_fused_long_frames_many_frames_per_cta(bins, fmt, overlap, iq_gain):
-    """32k and 64k frames run in ONE kernel (MODE_FUSED*: the samples and the window reach shared memory
-    through a ring of cp.async.bulk stages, radix-2/4 step, then 2/4 16k transforms per frame).  Enough
+    """32k frames (int16, float32) and 64k frames (int16) run in ONE kernel (MODE_FUSED*: the samples and the window
+    reach shared memory through a ring of cp.async.bulk stages, radix-2/4 step, then 2/4 16k transforms per frame,
+    the waiting classes parked in tensor memory).  Enough
     frames that every CTA of the persistent grid walks several of them: the ring's mbarrier phases, the
     stages that live in the magnitude stash and the CTA-private scratch are all reused.  The last case
     has a hop that is not a multiple of 4 samples: no 16-byte aligned frame starts, so the split path
@@ -150,7 +151,12 @@ def test_fused_long_frames_many_frames_per_cta(bins, fmt, overlap, iq_gain):
         iq, in_format = synth.generate_float32(spec), ro.IN_FLOAT32
     wf = ro.Waterfall(bins, overlap, sample_rate=96000, in_format=in_format, iq_gain=iq_gain)
     rows, _, nf = wf.process_host(iq)
+    kernel = wf.kernel_name()
     wf.close()
+    if hop % 4 == 0 and (bins == 32768 or fmt == "int16"):
+        assert "MODE_FUSED" in kernel, kernel           # 32k: MODE_FUSED1 / _F32; 64k int16: MODE_FUSED2
+    else:
+        assert "MODE_SPLIT" in kernel, kernel
     ref = R.waterfall_rows(iq, bins, overlap, iq_gain=iq_gain)
     assert nf == len(ref) == n_frames
     assert_rows_close(rows, ref, f"{fmt} fused N={bins} ov={overlap}")
@@ -174,7 +180,8 @@ def test_long_frames_four_classes_stored_together(bins, hop, fmt, iq_gain):
         iq, in_format = synth.generate_int16(spec), ro.IN_INT16
     else:
         iq, in_format = synth.generate_float32(spec), ro.IN_FLOAT32
-    wf = ro.Waterfall(bins, bins - hop, sample_rate=96000, in_format=in_format, iq_gain=iq_gain)
+    # (64k int16 frames that start on 16-byte boundaries would take the fused kernel: the split path is asked for)
+    wf = ro.Waterfall(bins, bins - hop, sample_rate=96000, in_format=in_format, iq_gain=iq_gain, tuning=ro.TUNE_NO_FUSED)
     d_in, d_rows = DeviceBuffer(iq.nbytes), DeviceBuffer(4 * bins * n_frames)
     try:
         d_in.upload(iq)

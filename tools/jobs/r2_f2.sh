@@ -1,0 +1,16 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 300 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "65536 or fused" 2>&1 | tail -8
+timeout 200 python tools/stress_determinism.py 2>&1 | tail -3
+for rep in 1 2; do
+for tun in 0 1; do
+  echo "## variant tuning$tun rep $rep"
+  timeout 300 python tools/sweep.py --lo 16 --hi 16 --fmt int16 --tuning $tun | python -c "
+import sys, json
+for l in sys.stdin:
+    try: j = json.loads(l)
+    except Exception: continue
+    print(j.get('bins'), j.get('overlap'), round(j.get('Mframes_per_s', 0), 3), round(j.get('hbm_frac', 0), 4))
+"
+done
+done
