@@ -569,7 +569,15 @@ wf_fft2_kernel(const Wf2Params p)
 	// 16 KB (24 KB with window) for int16, 16 KB (20 KB) for float32
 	// (Na = 4: eight sample runs and four window runs -- q = 0, 1 at either end; q = 2, 3 are their mirror images --
 	// of one position each: 24 KB)
-	constexpr unsigned int SB = 2u * FNA * RUN_RAW + (WIN_TMEM ? 0u : (unsigned int)FNA * RUN_WIN);
+	// Na = 4 with WIN_LDG: the window values come by LDG one burst ahead instead (no mirror trick, four loads per
+	// position), so that a stage is 16 KB of samples and the ring has 2 + 4 stages like the Na = 2 one.
+	// -DRO_FUSED2_WIN_LDG=0: window runs in the bursts, 1 + 2 stages of 24 KB (A/B).
+#ifndef RO_FUSED2_WIN_LDG
+#define RO_FUSED2_WIN_LDG 1
+#endif
+	constexpr bool WIN_LDG = RO_FUSED2_WIN_LDG && FLA == 2;
+	constexpr bool WIN_RUNS = !WIN_TMEM && !WIN_LDG;               // window runs travel with the bursts
+	constexpr unsigned int SB = 2u * FNA * RUN_RAW + (WIN_RUNS ? (unsigned int)FNA * RUN_WIN : 0u);
 	// ring: ND stages of memory of their own (filled a whole frame ahead), NS more in the magnitude stash (filled at
 	// the start of the load phase); 1 + 2 with the window runs in the bursts, 2 + 4 without.  -DRO_FUSED_RING3=1: 1 + 2.
 #ifndef RO_FUSED_RING3
@@ -594,10 +602,13 @@ wf_fft2_kernel(const Wf2Params p)
 			mbar_wait(emptyb + s, ((fullph >> s) & 1u) ^ 1u);
 			if (lane == 0) mbar_expect_tx(fullb + s, SB);
 			__syncwarp();
-			if (lane < (WIN_TMEM ? 2 * FNA : 3 * FNA)) {
+			if (lane < (WIN_RUNS ? 3 * FNA : 2 * FNA)) {
 				const int pos0 = (lane & 1) ? R1 - (b + 1) * HP : b * HP;      // odd lanes: the high end
 				unsigned char *dst = stage_ptr(s);
 				if (lane < 2 * FNA)      // sample run q = lane / 2
+					// (Na = 4 re-reads three quarters of a frame's samples 90 us later, by which time L2 has let them go:
+					// ncu 302 KB from HBM per frame for 64 KB of new samples.  Loading them with an evict-last policy
+					// measured 2 % SLOWER, profiles/r02_fused64k_ab.txt.)
 					bulk_g2s(dst + lane * RUN_RAW,
 					         reinterpret_cast<const unsigned char *>(p.raw) + (fr * hop + (long long)(lane >> 1) * N + pos0 * M) * RAWB,
 					         RUN_RAW, fullb + s);
@@ -670,10 +681,24 @@ wf_fft2_kernel(const Wf2Params p)
 				const c64 wt1 = __ldg(twb + t);
 				c64 wt2 = wt1, wt3 = wt1;
 				if (FLA == 2) { wt2 = __ldg(twb + 2 * t); wt3 = __ldg(twb + 3 * t); }
+				float wnext[2 * HP][NA];               // WIN_LDG: the window values of the next burst
+				if constexpr (WIN_LDG) {
+#pragma unroll
+					for (int jj = 0; jj < 2 * HP; jj++)
+#pragma unroll
+						for (int q = 0; q < NA; q++)
+							wnext[jj][q] = __ldg(p.window_full + q * N + (jj < HP ? jj : R1 - HP + (jj - HP)) * M + t);
+				}
 #pragma unroll
 				for (int b = 0; b < NB; b++) {
 					raw_t raw[2 * HP][NA];
 					float wv[2 * HP][NA];
+					if constexpr (WIN_LDG) {
+#pragma unroll
+						for (int jj = 0; jj < 2 * HP; jj++)
+#pragma unroll
+							for (int q = 0; q < NA; q++) wv[jj][q] = wnext[jj][q];
+					}
 					if (b == 0) {
 						// the stash of the previous frame has been read by every warp: bursts ND .. NST-1 may land in it
 						if (t < 32) {
@@ -706,7 +731,7 @@ wf_fft2_kernel(const Wf2Params p)
 								raw[j][q] = rr[(2 * q) * HP * M + j * M + t];
 								raw[HP + j][q] = rr[(2 * q + 1) * HP * M + j * M + t];
 							}
-							if constexpr (!WIN_TMEM) {
+							if constexpr (WIN_RUNS) {
 								// window runs q = 0 .. Na/2-1 at either end; q >= Na/2 is the mirror image of q' = Na-1-q at
 								// the OTHER end: w[q*N + m] = w[q'*N + (N-1-m)]
 #pragma unroll
@@ -725,6 +750,15 @@ wf_fft2_kernel(const Wf2Params p)
 							for (int j = 0; j < HP; j++) {
 								wv[j][0] = wlo[2 * j]; wv[j][1] = wlo[2 * j + 1];
 								wv[HP + j][0] = whi[2 * j]; wv[HP + j][1] = whi[2 * j + 1];
+							}
+						}
+						if constexpr (WIN_LDG) {
+							if (b + 1 < NB) {
+#pragma unroll
+								for (int jj = 0; jj < 2 * HP; jj++)
+#pragma unroll
+									for (int q = 0; q < NA; q++)
+										wnext[jj][q] = __ldg(p.window_full + q * N + (jj < HP ? (b + 1) * HP + jj : R1 - (b + 2) * HP + (jj - HP)) * M + t);
 							}
 						}
 					}

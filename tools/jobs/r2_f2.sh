@@ -1,11 +1,12 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "65536 or fused" 2>&1 | tail -8
+timeout 300 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "65536 or fused" 2>&1 | tail -3
 timeout 200 python tools/stress_determinism.py 2>&1 | tail -3
 for rep in 1 2; do
-for tun in 0 1; do
-  echo "## variant tuning$tun rep $rep"
-  timeout 300 python tools/sweep.py --lo 16 --hi 16 --fmt int16 --tuning $tun | python -c "
+for v in nol2 l2; do
+  if [ $v = l2 ]; then unset RO_CUDA_LIB; else export RO_CUDA_LIB=$PWD/radio_observer_b200/csrc/_obj/libro_cuda_$v.so; fi
+  echo "## variant $v rep $rep"
+  timeout 300 python tools/sweep.py --lo 16 --hi 16 --fmt int16 | python -c "
 import sys, json
 for l in sys.stdin:
     try: j = json.loads(l)
