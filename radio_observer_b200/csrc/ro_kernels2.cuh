@@ -38,7 +38,7 @@ namespace ro {
 #define RO_TRACE_NP 20
 static __device__ unsigned long long ro_trace_buf[2 * RO_TRACE_NF * 16 * RO_TRACE_NP];
 #define RO_TP(i) do { \
-	if ((MODE == MODE_STAGED || MODE == MODE_SPLIT) && LOG2N == 14 && (t & 31) == 0 && f - f0 >= RO_TRACE_F0 && f - f0 < RO_TRACE_F0 + RO_TRACE_NF && \
+	if ((MODE == MODE_STAGED || MODE == MODE_SPLIT || MODE == MODE_FUSED2) && LOG2N == 14 && (t & 31) == 0 && f - f0 >= RO_TRACE_F0 && f - f0 < RO_TRACE_F0 + RO_TRACE_NF && \
 	    (blockIdx.x == 0 || blockIdx.x == 73)) \
 		ro_trace_buf[(((blockIdx.x ? 1 : 0) * RO_TRACE_NF + (int)(f - f0) - RO_TRACE_F0) * 16 + (t >> 5)) * RO_TRACE_NP + (i)] = clock64(); \
 } while (0)
@@ -669,6 +669,7 @@ wf_fft2_kernel(const Wf2Params p)
 			constexpr int NA = FNA;
 			constexpr int NBIG = N << FLA;
 			const int r = (int)(f & (NA - 1));
+			RO_TP(0);
 			// Na = 2: one class parked (tensor memory, or (Na-1) slices of global memory without it); Na = 4: classes
 			// 1 and 2 in the two halves of the thread's tensor memory, class 3 in ONE slice of global memory
 			unsigned long long *scr = p.scratch + (size_t)blockIdx.x * (FLA == 2 ? 1 : NA - 1) * N;
@@ -1177,7 +1178,7 @@ wf_fft2_kernel(const Wf2Params p)
 					}
 				}
 				}
-				if (MODE == MODE_SPLIT) RO_TP(16);
+				if (MODE == MODE_SPLIT || MODE == MODE_FUSED2) RO_TP(16);
 				if constexpr (FUSED) {
 					// the last class of the frame has read the stash: its 64 KB may stage the next frame
 					if (r == FNA - 1) {

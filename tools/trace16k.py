@@ -60,8 +60,9 @@ def main():
     out = {}
     for cta in range(2):
         T = tr[cta]
+        out["cta%d" % cta] = T.tolist()
         if T.min() == 0:
-            print("cta slot %d: incomplete trace" % cta)
+            print("cta slot %d: not every boundary is stamped in this mode (raw trace in the JSON)" % cta)
             continue
         frame_len = np.diff(T[:, :, 6], axis=0)            # barrier A to barrier A, per warp
         print("\n== CTA slot %d: frame period (barrier A to barrier A) %.0f clk mean, min %d max %d" %
@@ -84,7 +85,6 @@ def main():
         for i in list(range(0, 7)):
             lv = [rel2[:, l * 4:(l + 1) * 4, i].mean() for l in range(4)]
             print("%-28s %7.0f %7.0f %7.0f %7.0f   (next frame)" % (NAMES[i], *lv))
-        out["cta%d" % cta] = T.tolist()
     if a.json:
         json.dump(dict(names=NAMES, trace=out), open(a.json, "w"))
 
