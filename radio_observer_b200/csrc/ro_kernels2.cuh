@@ -797,6 +797,8 @@ wf_fft2_kernel(const Wf2Params p)
 					// the values are in registers and used: the stage may be refilled
 					__syncwarp();
 					if ((t & 31) == 0) mbar_arrive(emptyb + s);
+					if (b == NB / 2 - 1) RO_TP(18);
+					if (b == NB - 1) RO_TP(19);
 				}
 #if RO_L2_PREFETCH
 				if (f + NA < f1) {     // the hop new samples of the next frame
@@ -893,9 +895,26 @@ wf_fft2_kernel(const Wf2Params p)
 
 		// ---- pass 1 ----
 		RO_TP(2);
+		// The fused 64k kernel has no registers to spare for ten twiddle bases that live as long as the CTA (ptxas
+		// spilled 312 bytes per thread, and pass 1 of class 0 spent 5 k clk behind the parked class's stores waiting
+		// for spilled bases, profiles/r02_trace_fused64k_timeline.txt): it fetches the five of a pass again, one
+		// transform ahead of their use (36 bytes of spills left; 3.17 -> 3.29 M frames/s at 75 % overlap).  The same
+		// in the other long-frame kernels: fused 32k -13 %, split path +-2 %, so not there.  -DRO_RELOAD_BASES=0: A/B.
+#ifndef RO_RELOAD_BASES
+#define RO_RELOAD_BASES 1
+#endif
+		constexpr bool RELOAD_B = RO_RELOAD_BASES && FLA == 2;
+		c64 bb[LP];
+		if constexpr (RELOAD_B) {
+			const unsigned long long *tw64 = reinterpret_cast<const unsigned long long *>(p.tw);
+#pragma unroll
+			for (int i = 0; i < LP; i++) bb[i] = __ldg(tw64 + ((t << i) & NMASK));
+		}
 		fft_fwd2<R1, USE_DIT>(v);
+		RO_TP(17);
 		RO_SITE(0, p.stagger & 1);
 		if (TW_TMEM) twiddle_tmem(v, 0u);
+		else if (RELOAD_B) twiddle_powers2<R1>(v, bb);
 		else twiddle_powers2<R1>(v, b1);
 		RO_SITE(1, p.stagger & 1);
 		RO_TP(3);
@@ -955,9 +974,15 @@ wf_fft2_kernel(const Wf2Params p)
 			if (CHAIN && (p.stagger & 2)) chain_pass(wq, wl, LEVELS, cdist);
 			split_arrive(bar_rd2, t);                   // my pass-2 inputs are in registers
 			RO_TP(8);
+			if constexpr (RELOAD_B) {
+				const unsigned long long *tw64 = reinterpret_cast<const unsigned long long *>(p.tw);
+#pragma unroll
+				for (int i = 0; i < LP; i++) bb[i] = __ldg(tw64 + (((n3 * P) << i) & NMASK));
+			}
 			fft_fwd2<R2, USE_DIT>(v);
 			RO_SITE(2, p.stagger & 1);
 			if (TW_TMEM) twiddle_tmem(v, 2u * P);
+			else if (RELOAD_B) twiddle_powers2<R2>(v, bb);
 			else twiddle_powers2<R2>(v, b2);
 			RO_SITE(3, p.stagger & 1);
 			RO_TP(9);

@@ -56,7 +56,7 @@ def main():
     buf = np.zeros(2 * NF * NW * NP, dtype=np.uint64)
     rc = lib.ro_trace_dump(buf.ctypes.data, buf.size)
     assert rc == 0, rc
-    tr = buf.reshape(2, NF, NW, NP)[..., :17].astype(np.int64)
+    tr = buf.reshape(2, NF, NW, NP).astype(np.int64)
     out = {}
     for cta in range(2):
         T = tr[cta]
