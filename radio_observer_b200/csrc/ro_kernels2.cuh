@@ -382,6 +382,12 @@ wf_fft2_kernel(const Wf2Params p)
 	// The host never asks for more resident CTAs than 512 columns allow (v2_tmem_cols, ro_cuda.cu).
 	constexpr bool TW_TMEM = RO_TW_TMEM && !SPLIT && wf2_tmem_cols<LOG2N, P, MODE>() > 0;
 	constexpr bool USE_TMEM = SPLIT_TMEM || FUSED_TMEM || TW_TMEM;
+	// The split path's kernel has 24 words of tensor memory to spare (columns 56..63, 88..95, 120..127 are used
+	// neither by parked pairs nor by parked fours): its ten twiddle bases wait there instead of in registers that
+	// ptxas spills.  -DRO_SPLIT_BASES_TMEM=0: registers (A/B).
+#ifndef RO_SPLIT_BASES_TMEM
+#define RO_SPLIT_BASES_TMEM 1
+#endif
 	// rows of the next item prefetched into shared memory (needs the four-class stores: p.pair == 2)
 	constexpr int LROWS = SPLIT_TMEM ? wf2_split_lrows<LOG2N, P, R3, MODE>() : 0;
 	static_assert(SPLIT_TMEM || wf2_split_lrows<LOG2N, P, R3, MODE>() == 0, "the landing area is the stash: parked magnitudes must be in tensor memory");
@@ -494,6 +500,19 @@ wf_fft2_kernel(const Wf2Params p)
 		}
 	}
 	const c64 gain2 = pk(0.f, p.iq_gain);
+	if constexpr (RO_SPLIT_BASES_TMEM && SPLIT_TMEM && LP == 5) {
+		float q8[8];
+		float lo, hi;
+#pragma unroll
+		for (int i = 0; i < 4; i++) { upk(b1[i], lo, hi); q8[2 * i] = lo; q8[2 * i + 1] = hi; }
+		tmem_st8(tmem + 56u, q8);
+#pragma unroll
+		for (int i = 0; i < 4; i++) { upk(b2[i], lo, hi); q8[2 * i] = lo; q8[2 * i + 1] = hi; }
+		tmem_st8(tmem + 120u, q8);
+		const c64 last[2] = {b1[4], b2[4]};
+		tmem_st_c64(tmem + 88u, last);          // b1[4] at 88..89, b2[4] at 90..91
+		tmem_wait_st();
+	}
 	if constexpr (TW_TMEM) {
 		c64 w[P];
 		twiddle_table2<R1>(w, b1);
@@ -904,7 +923,17 @@ wf_fft2_kernel(const Wf2Params p)
 #define RO_RELOAD_BASES 1
 #endif
 		constexpr bool RELOAD_B = RO_RELOAD_BASES && FLA == 2;
+		constexpr bool TMEM_B = RO_SPLIT_BASES_TMEM && SPLIT_TMEM && LP == 5;
 		c64 bb[LP];
+		if constexpr (TMEM_B) {
+			float q8[8], q2[2];
+			tmem_ld_f(tmem + 56u, q8);
+			tmem_ld_f(tmem + 88u, q2);
+			tmem_wait_ld();
+#pragma unroll
+			for (int i = 0; i < 4; i++) bb[i] = pk(q8[2 * i], q8[2 * i + 1]);
+			bb[4] = pk(q2[0], q2[1]);
+		}
 		if constexpr (RELOAD_B) {
 			const unsigned long long *tw64 = reinterpret_cast<const unsigned long long *>(p.tw);
 #pragma unroll
@@ -914,7 +943,7 @@ wf_fft2_kernel(const Wf2Params p)
 		RO_TP(17);
 		RO_SITE(0, p.stagger & 1);
 		if (TW_TMEM) twiddle_tmem(v, 0u);
-		else if (RELOAD_B) twiddle_powers2<R1>(v, bb);
+		else if (RELOAD_B || TMEM_B) twiddle_powers2<R1>(v, bb);
 		else twiddle_powers2<R1>(v, b1);
 		RO_SITE(1, p.stagger & 1);
 		RO_TP(3);
@@ -974,6 +1003,15 @@ wf_fft2_kernel(const Wf2Params p)
 			if (CHAIN && (p.stagger & 2)) chain_pass(wq, wl, LEVELS, cdist);
 			split_arrive(bar_rd2, t);                   // my pass-2 inputs are in registers
 			RO_TP(8);
+			if constexpr (TMEM_B) {
+				float q8[8], q2[2];
+				tmem_ld_f(tmem + 120u, q8);
+				tmem_ld_f(tmem + 90u, q2);
+				tmem_wait_ld();
+#pragma unroll
+				for (int i = 0; i < 4; i++) bb[i] = pk(q8[2 * i], q8[2 * i + 1]);
+				bb[4] = pk(q2[0], q2[1]);
+			}
 			if constexpr (RELOAD_B) {
 				const unsigned long long *tw64 = reinterpret_cast<const unsigned long long *>(p.tw);
 #pragma unroll
@@ -982,7 +1020,7 @@ wf_fft2_kernel(const Wf2Params p)
 			fft_fwd2<R2, USE_DIT>(v);
 			RO_SITE(2, p.stagger & 1);
 			if (TW_TMEM) twiddle_tmem(v, 2u * P);
-			else if (RELOAD_B) twiddle_powers2<R2>(v, bb);
+			else if (RELOAD_B || TMEM_B) twiddle_powers2<R2>(v, bb);
 			else twiddle_powers2<R2>(v, b2);
 			RO_SITE(3, p.stagger & 1);
 			RO_TP(9);
