@@ -84,6 +84,8 @@ __host__ __device__ constexpr bool mode_is_split(int m) { return m == MODE_SPLIT
 __host__ __device__ constexpr bool mode_is_f32(int m) { return m == MODE_DIRECT_F32 || m == MODE_FUSED1_F32; }
 // MODE_FUSED*: bytes of the raw-sample / window staging ring beside the 64 KB stash, and of its barriers
 constexpr size_t FUSED_RING_BYTES = 32768, FUSED_BAR_BYTES = 512;
+// ... and of the table of pass-2 twiddle bases of the 32k kernels (16 values of n3 x 5 bases), see pass 2
+constexpr size_t FUSED_B2_BYTES = 16 * 5 * 8;
 template <bool F32IN> struct raw_word { typedef unsigned int type; };          // one int16 I/Q pair
 template <> struct raw_word<true> { typedef unsigned long long type; };       // one float32 I/Q pair
 
@@ -329,7 +331,7 @@ constexpr size_t wf2_smem_bytes()
 	constexpr size_t PAD1 = (R3 < 16 && !(R3 == 8 && P == 32)) ? R3 : 0;   // 8k: swizzled instead of padded, see the kernel
 	return sizeof(c64) * (N + P * PAD1) + (mode_is_split(MODE) ? 0 : sizeof(float) * (N / 2)) + 32 +
 	       (MODE == MODE_STAGED ? 4 * N : 0) + (mode_is_split(MODE) && P / R3 >= 2 ? 4 * N : 0) +
-	       (mode_is_fused(MODE) ? FUSED_RING_BYTES + FUSED_BAR_BYTES : 0) +
+	       (mode_is_fused(MODE) ? FUSED_RING_BYTES + FUSED_BAR_BYTES + FUSED_B2_BYTES : 0) +
 	       (wf2_split_lrows<LOG2N, P, R3, MODE>() > 16 ? sizeof(c64) * (N / P) * (wf2_split_lrows<LOG2N, P, R3, MODE>() - 16) : 0);
 }
 
@@ -500,6 +502,18 @@ wf_fft2_kernel(const Wf2Params p)
 		}
 	}
 	const c64 gain2 = pk(0.f, p.iq_gain);
+	// Fused 32k kernels: tensor memory is full (parked class + window) and ptxas spills 100 .. 120 bytes; the
+	// pass-2 bases depend on n3 = t % 16 only, so they are read from a 640-byte table in shared memory per pass
+	// instead of living in ten registers.  -DRO_FUSED_B2_SMEM=0: registers (A/B).
+#ifndef RO_FUSED_B2_SMEM
+#define RO_FUSED_B2_SMEM 1
+#endif
+	constexpr bool B2_SMEM = RO_FUSED_B2_SMEM && FUSED && FLA == 1 && LP == 5 && R3 == 16;
+	c64 *b2tab = reinterpret_cast<c64 *>(reinterpret_cast<unsigned char *>(mbar + 4) + 4 * N + FUSED_RING_BYTES + FUSED_BAR_BYTES);
+	if constexpr (B2_SMEM) {
+		if (t < 16 * LP) b2tab[t] = __ldg(reinterpret_cast<const unsigned long long *>(p.tw) + ((((t / LP) * P) << (t % LP)) & NMASK));
+		__syncthreads();
+	}
 	if constexpr (RO_SPLIT_BASES_TMEM && SPLIT_TMEM && LP == 5) {
 		float q8[8];
 		float lo, hi;
@@ -1017,10 +1031,14 @@ wf_fft2_kernel(const Wf2Params p)
 #pragma unroll
 				for (int i = 0; i < LP; i++) bb[i] = __ldg(tw64 + (((n3 * P) << i) & NMASK));
 			}
+			if constexpr (B2_SMEM) {
+#pragma unroll
+				for (int i = 0; i < LP; i++) bb[i] = b2tab[n3 * LP + i];
+			}
 			fft_fwd2<R2, USE_DIT>(v);
 			RO_SITE(2, p.stagger & 1);
 			if (TW_TMEM) twiddle_tmem(v, 2u * P);
-			else if (RELOAD_B || TMEM_B) twiddle_powers2<R2>(v, bb);
+			else if (RELOAD_B || TMEM_B || B2_SMEM) twiddle_powers2<R2>(v, bb);
 			else twiddle_powers2<R2>(v, b2);
 			RO_SITE(3, p.stagger & 1);
 			RO_TP(9);
