@@ -508,7 +508,7 @@ wf_fft2_kernel(const Wf2Params p)
 #ifndef RO_FUSED_B2_SMEM
 #define RO_FUSED_B2_SMEM 1
 #endif
-	constexpr bool B2_SMEM = RO_FUSED_B2_SMEM && FUSED && FLA == 1 && LP == 5 && R3 == 16;
+	constexpr bool B2_SMEM = RO_FUSED_B2_SMEM && FUSED && LP == 5 && R3 == 16;        // (64k: pass 1's bases still come by LDG)
 	c64 *b2tab = reinterpret_cast<c64 *>(reinterpret_cast<unsigned char *>(mbar + 4) + 4 * N + FUSED_RING_BYTES + FUSED_BAR_BYTES);
 	if constexpr (B2_SMEM) {
 		if (t < 16 * LP) b2tab[t] = __ldg(reinterpret_cast<const unsigned long long *>(p.tw) + ((((t / LP) * P) << (t % LP)) & NMASK));
@@ -1026,7 +1026,7 @@ wf_fft2_kernel(const Wf2Params p)
 				for (int i = 0; i < 4; i++) bb[i] = pk(q8[2 * i], q8[2 * i + 1]);
 				bb[4] = pk(q2[0], q2[1]);
 			}
-			if constexpr (RELOAD_B) {
+			if constexpr (RELOAD_B && !B2_SMEM) {
 				const unsigned long long *tw64 = reinterpret_cast<const unsigned long long *>(p.tw);
 #pragma unroll
 				for (int i = 0; i < LP; i++) bb[i] = __ldg(tw64 + (((n3 * P) << i) & NMASK));
